@@ -1,0 +1,579 @@
+// fluid_sim.cu — the FluidSim handle and the C ABI of include/fluid_b200.h.
+//
+// Host-side mirror of the reference's FluidSimulation (src/simulation.rs): owns the particle store
+// (structure of arrays in HBM), the reference-compatible start_indices table, the force-field texture
+// and one CUDA stream, and enqueues the per-tick kernel sequence
+//   predict+key+histogram -> scan -> onesweep x P -> gather+cell tables -> density -> force+integrate
+// in place of the reference's K1, K2, K3 x S(S+1)/2, K4, K5, K6 dispatches (src/simulation.rs:512-537).
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels_cells.cuh"
+#include "kernels_hash.cuh"
+#include "kernels_sph.cuh"
+#include "radix_sort.cuh"
+#include "sim_internal.h"
+
+namespace fluid {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+    char buf[512];
+    snprintf(buf, sizeof buf, "CUDA error %d (%s) at %s:%d in %s", (int)e, cudaGetErrorString(e), file, line, what);
+    g_last_error = buf;
+    cudaGetLastError();
+    return FLUID_ERR_CUDA;
+}
+static int invalid(const char* msg) {
+    g_last_error = msg;
+    return FLUID_ERR_INVALID_ARGUMENT;
+}
+
+// Rust f32::powi (compiler-rt __powisf2), used by the uniform derivation src/simulation.rs:486-490
+static float powi_f32(float a, int b) {
+    float r = 1.0f;
+    for (;;) {
+        if (b & 1) r *= a;
+        b /= 2;
+        if (b == 0) break;
+        a *= a;
+    }
+    return r;
+}
+
+// ---- AoS <-> SoA transposition at the boundary (ParticleInstance, src/simulation.rs:126-135) ----
+__global__ void k_aos_to_soa(const FluidParticle* __restrict__ aos, uint32_t n, float2* __restrict__ pos,
+                             float2* __restrict__ pred, float2* __restrict__ vel, float* __restrict__ rho,
+                             uint32_t* __restrict__ keys) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4* src = reinterpret_cast<const float4*>(aos + i);
+    float4 lo = __ldg(src), hi = __ldg(src + 1);
+    pos[i] = make_float2(lo.x, lo.y);
+    pred[i] = make_float2(lo.z, lo.w);
+    vel[i] = make_float2(hi.x, hi.y);
+    rho[i] = hi.z;
+    keys[i] = __float_as_uint(hi.w);
+}
+__global__ void k_soa_to_aos(FluidParticle* __restrict__ aos, uint32_t n, const float2* __restrict__ pos,
+                             const float2* __restrict__ pred, const float2* __restrict__ vel,
+                             const float* __restrict__ rho, const uint32_t* __restrict__ keys) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float2 a = pos[i], b = pred[i], c = vel[i];
+    float4* dst = reinterpret_cast<float4*>(aos + i);
+    dst[0] = make_float4(a.x, a.y, b.x, b.y);
+    dst[1] = make_float4(c.x, c.y, rho[i], __uint_as_float(keys[i]));
+}
+
+static uint32_t bits_for(uint32_t max_value) {
+    uint32_t b = 0;
+    while (b < 32 && (max_value >> b) != 0) b++;
+    return b == 0 ? 1 : b;
+}
+
+int Sim::alloc(uint32_t cap) {
+    // free old particle-sized buffers, allocate new; contents are NOT preserved
+    void** bufs[] = {(void**)&pos_a, (void**)&vel_a, (void**)&pos_s, (void**)&vel_s, (void**)&pred_s, (void**)&rho,
+                     (void**)&keys_u, (void**)&keys_b, (void**)&keys_c, (void**)&idx_a, (void**)&idx_b,
+                     (void**)&sort_scratch, (void**)&aos_stage, (void**)&dbg_accel, (void**)&dbg_abs};
+    for (void** b : bufs) { if (*b) cudaFree(*b); *b = nullptr; }
+    capacity = cap;
+    const size_t padded = (size_t)cap + 64;
+    FLUID_CUDA(cudaMalloc(&pos_a, padded * 8)); FLUID_CUDA(cudaMalloc(&vel_a, padded * 8));
+    FLUID_CUDA(cudaMalloc(&pos_s, padded * 8)); FLUID_CUDA(cudaMalloc(&vel_s, padded * 8));
+    FLUID_CUDA(cudaMalloc(&pred_s, padded * 8)); FLUID_CUDA(cudaMalloc(&rho, padded * 4));
+    FLUID_CUDA(cudaMalloc(&keys_u, padded * 4)); FLUID_CUDA(cudaMalloc(&keys_b, padded * 4));
+    FLUID_CUDA(cudaMalloc(&keys_c, padded * 4));
+    FLUID_CUDA(cudaMalloc(&idx_a, padded * 4)); FLUID_CUDA(cudaMalloc(&idx_b, padded * 4));
+    void* zero_me[] = {pos_a, vel_a, pos_s, vel_s, pred_s};
+    for (void* z : zero_me) FLUID_CUDA(cudaMemsetAsync(z, 0, padded * 8, stream));
+    void* zero_me4[] = {rho, keys_u, keys_b, keys_c, idx_a, idx_b};
+    for (void* z : zero_me4) FLUID_CUDA(cudaMemsetAsync(z, 0, padded * 4, stream));
+    max_tiles = (cap + SORT_TILE - 1) / SORT_TILE;
+    // [hist MAX_PASSES*256][tile counters MAX_PASSES, padded to 256][status MAX_PASSES*max_tiles*256]
+    sort_scratch_words = (size_t)MAX_PASSES * RADIX + RADIX + (size_t)MAX_PASSES * max_tiles * RADIX;
+    FLUID_CUDA(cudaMalloc(&sort_scratch, sort_scratch_words * 4));
+    keys_sorted = keys_b;
+    return FLUID_OK;
+}
+
+void Sim::make_uniform(const FluidTickSettings& t, uint32_t tick_value, FluidSimUniform* o) const {
+    // src/simulation.rs:470-497
+    const float PI_RS = 3.14159274101257324219f;
+    const float h = settings.smoothing_radius;
+    memset(o, 0, sizeof *o);
+    o->delta = t.delta;
+    o->particle_count = n;
+    o->sqr_radius = h * h;
+    o->frame_time = tick_value;
+    o->gravity[0] = t.gravity[0]; o->gravity[1] = t.gravity[1];
+    o->bounds[0] = settings.size[0]; o->bounds[1] = settings.size[1];
+    o->mouse_pos[0] = t.mouse_pos[0]; o->mouse_pos[1] = t.mouse_pos[1];
+    o->smoothing_radius = h;
+    o->particle_mass = t.mass;
+    o->pressure_constant = t.pressure_constant;
+    o->rest_density = t.rest_density;
+    o->damping_factor = t.damping_factor;
+    o->viscosity_coefficient = t.viscosity_coefficient;
+    o->surface_tension_treshold = t.surface_tension_treshold;
+    o->surface_tension_coefficient = t.surface_tension_coefficient;
+    o->poly6_kernel_volume = 4.0f / (PI_RS * powi_f32(h, 8));
+    o->poly6_kernel_derivative = 24.0f / (PI_RS * powi_f32(h, 8));
+    o->poly6_kernel_laplacian = 8.0f / (PI_RS * powi_f32(h, 8));
+    o->spiky_kernel_derivative = 12.0f / (powi_f32(h, 4) * PI_RS);
+    o->viscosity_kernel = 15.0f / (2.0f * PI_RS * powi_f32(h, 3));
+    o->mouse_state = t.mouse_state;
+    o->mouse_force_radius = t.mouse_force_radius;
+    o->mouse_force_power = t.mouse_force_power;
+    o->grid_w = grid_w;
+    o->grid_h = grid_h;
+    o->texture_size[0] = (float)settings.texture_size[0];
+    o->texture_size[1] = (float)settings.texture_size[1];
+}
+
+DevParams Sim::make_params(const FluidSimUniform& u) const {
+    DevParams p;
+    memset(&p, 0, sizeof p);
+    const float PI_WGSL = 3.14159265359f;  // funcs.wgsl:54
+    p.n = n;
+    p.grid_w = u.grid_w; p.grid_h = u.grid_h; p.num_cells = u.grid_w * u.grid_h;
+    p.dt = u.delta;
+    p.bounds_x = u.bounds[0]; p.bounds_y = u.bounds[1];
+    p.half_x = u.bounds[0] * 0.5f; p.half_y = u.bounds[1] * 0.5f;
+    p.h = u.smoothing_radius;
+    p.h2 = u.smoothing_radius * u.smoothing_radius;
+    p.mass = u.particle_mass;
+    p.poly6_norm = 4.0f / (PI_WGSL * powf(u.smoothing_radius, 8.0f));  // funcs.wgsl:76
+    p.pressure_constant = u.pressure_constant; p.rest_density = u.rest_density;
+    p.spiky = u.spiky_kernel_derivative;
+    p.visc_k = u.viscosity_kernel;
+    p.visc_coef = u.viscosity_coefficient;
+    p.two_h3 = 2.0f * u.smoothing_radius * u.smoothing_radius * u.smoothing_radius;
+    p.gravity_dt_x = u.gravity[0] * u.delta; p.gravity_dt_y = u.gravity[1] * u.delta;
+    p.damping = u.damping_factor;
+    p.one_minus_damping = 1.0f - u.damping_factor;
+    p.neg_damping = -1.0f * u.damping_factor;
+    p.mouse_state = u.mouse_state;
+    p.mouse_x = u.mouse_pos[0]; p.mouse_y = u.mouse_pos[1];
+    p.mouse_radius = u.mouse_force_radius; p.mouse_power = u.mouse_force_power;
+    p.mouse_state_f = (float)u.mouse_state;
+    p.tex_w = u.texture_size[0]; p.tex_h = u.texture_size[1];
+    p.tex_wu = settings.texture_size[0]; p.tex_hu = settings.texture_size[1];
+    p.tex_len = p.tex_wu * p.tex_hu;
+    p.p2w_x = (u.bounds[0] * 2.0f) / u.texture_size[0];
+    p.p2w_y = (u.bounds[1] * 2.0f) / u.texture_size[1];
+    return p;
+}
+
+void Sim::mark(const char* name) {
+    if (!timing) return;
+    if (n_marks >= MAX_MARKS) return;
+    if (!mark_events[n_marks]) cudaEventCreate(&mark_events[n_marks]);
+    cudaEventRecord(mark_events[n_marks], stream);
+    mark_names[n_marks] = name;
+    n_marks++;
+}
+
+template <int PASSES>
+static void launch_hash(Sim* s, const DevParams& p, uint32_t* hist) {
+    const uint32_t pairs = (p.n + 1) / 2;
+    uint32_t blocks = (pairs + HASH_THREADS - 1) / HASH_THREADS;
+    const uint32_t max_blocks = (uint32_t)s->num_sms * 8u;
+    if (blocks > max_blocks) blocks = max_blocks;
+    k_predict_key_hist<PASSES><<<blocks, HASH_THREADS, 0, s->stream>>>(p, s->pos_a, s->vel_a, s->keys_u, hist, s->d_frame_time);
+}
+
+int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
+    tick += 1;  // src/simulation.rs:460
+    make_uniform(t, tick, &last_uniform);
+    const DevParams p = make_params(last_uniform);
+    n_marks = 0;
+    mark("begin");
+
+    const uint32_t passes = sort_passes;
+    const uint32_t tiles = (n + SORT_TILE - 1) / SORT_TILE;
+    uint32_t* hist = sort_scratch;
+    uint32_t* counters = sort_scratch + MAX_PASSES * RADIX;
+    uint32_t* status = counters + RADIX;
+    // one memset clears histograms, tile tickets and the look-back status words of the passes in use
+    FLUID_CUDA(cudaMemsetAsync(sort_scratch, 0, ((size_t)MAX_PASSES * RADIX + RADIX + (size_t)passes * tiles * RADIX) * 4, stream));
+
+    switch (passes) {
+        case 1: launch_hash<1>(this, p, hist); break;
+        case 2: launch_hash<2>(this, p, hist); break;
+        case 3: launch_hash<3>(this, p, hist); break;
+        default: launch_hash<4>(this, p, hist); break;
+    }
+    launches++;
+    mark("predict+key+hist");
+    k_scan_histograms<<<passes, RADIX, 0, stream>>>(hist);
+    launches++;
+
+    const size_t sort_smem = (size_t)SORT_TILE * 2 * sizeof(uint32_t);
+    const uint32_t* kin = keys_u;
+    const uint32_t* vin = nullptr;
+    uint32_t* kout = keys_b;
+    uint32_t* vout = idx_a;
+    for (uint32_t q = 0; q < passes; q++) {
+        if (q == 0)
+            k_onesweep_pass<SORT_ITEMS, true><<<tiles, SORT_THREADS, sort_smem, stream>>>(
+                kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, n, (int)(q * RADIX_BITS));
+        else
+            k_onesweep_pass<SORT_ITEMS, false><<<tiles, SORT_THREADS, sort_smem, stream>>>(
+                kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, n, (int)(q * RADIX_BITS));
+        launches++;
+        kin = kout; vin = vout;
+        kout = (kout == keys_b) ? keys_c : keys_b;
+        vout = (vout == idx_a) ? idx_b : idx_a;
+    }
+    keys_sorted = const_cast<uint32_t*>(kin);
+    idx_sorted = const_cast<uint32_t*>(vin);
+    mark("sort");
+
+    const uint32_t gblocks = (n + GATHER_THREADS - 1) / GATHER_THREADS;
+    k_gather_cells<<<gblocks, GATHER_THREADS, 0, stream>>>(p, keys_sorted, idx_sorted, pos_a, vel_a, pos_s, pred_s, vel_s,
+                                                         start_indices, cell_lb, quirk);
+    launches++;
+    mark("gather+cells");
+    if (hash_sort_only) {
+        // state stays consistent for download: positions/velocities unchanged, in sorted order
+        FLUID_CUDA(cudaMemcpyAsync(pos_a, pos_s, (size_t)n * 8, cudaMemcpyDeviceToDevice, stream));
+        FLUID_CUDA(cudaMemcpyAsync(vel_a, vel_s, (size_t)n * 8, cudaMemcpyDeviceToDevice, stream));
+        mark("copy");
+        FLUID_CUDA(cudaGetLastError());
+        return FLUID_OK;
+    }
+    const uint32_t sblocks = (n + SPH_THREADS - 1) / SPH_THREADS;
+    k_density<<<sblocks, SPH_THREADS, 0, stream>>>(p, pred_s, keys_sorted, cell_lb, quirk, rho);
+    launches++;
+    mark("density");
+    if (debug_force)
+        k_force_integrate<true><<<sblocks, SPH_THREADS, 0, stream>>>(p, pos_s, pred_s, vel_s, rho, keys_sorted, cell_lb, quirk,
+                                                                   force_field, d_frame_time, pos_a, vel_a, dbg_accel, dbg_abs);
+    else
+        k_force_integrate<false><<<sblocks, SPH_THREADS, 0, stream>>>(p, pos_s, pred_s, vel_s, rho, keys_sorted, cell_lb, quirk,
+                                                                    force_field, d_frame_time, pos_a, vel_a, nullptr, nullptr);
+    launches++;
+    mark("force+integrate");
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+
+}  // namespace fluid
+
+using namespace fluid;
+
+extern "C" {
+
+const char* fluid_last_error(void) { return g_last_error.c_str(); }
+int fluid_abi_version(void) { return FLUID_B200_ABI_VERSION; }
+int fluid_device_count(void) {
+    int c = 0;
+    cudaError_t e = cudaGetDeviceCount(&c);
+    if (e != cudaSuccess) { cuda_fail(e, "cudaGetDeviceCount", __FILE__, __LINE__); return FLUID_ERR_NO_DEVICE; }
+    return c;
+}
+
+int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** out) {
+    if (!s || !out) return invalid("fluid_sim_create: null argument");
+    *out = nullptr;
+    if (s->particle_count < 2) return invalid("fluid_sim_create: particle_count < 2 (the reference panics: (0).ilog2(), src/simulation.rs:323-324)");
+    if (!(s->smoothing_radius > 0.0f) || !(s->size[0] > 0.0f) || !(s->size[1] > 0.0f))
+        return invalid("fluid_sim_create: smoothing_radius and size must be positive");
+    if (s->texture_size[0] == 0 || s->texture_size[1] == 0) return invalid("fluid_sim_create: texture_size must be non-zero");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+        cudaGetLastError();
+        set_error("fluid_sim_create: no CUDA device available (this library has no CPU fallback)");
+        return FLUID_ERR_NO_DEVICE;
+    }
+    if (device_ordinal < 0 || device_ordinal >= count) { set_error("fluid_sim_create: device ordinal out of range"); return FLUID_ERR_NO_DEVICE; }
+    FLUID_CUDA(cudaSetDevice(device_ordinal));
+    cudaDeviceProp prop;
+    FLUID_CUDA(cudaGetDeviceProperties(&prop, device_ordinal));
+    if (prop.major < 10) { set_error("fluid_sim_create: device is not sm_100+ (library is built for sm_100a only)"); return FLUID_ERR_NO_DEVICE; }
+
+    Sim* sim = new Sim();
+    sim->device = device_ordinal;
+    sim->num_sms = prop.multiProcessorCount;
+    sim->settings = *s;
+    sim->n = s->particle_count;
+    // src/simulation.rs:140-141
+    sim->grid_w = (uint32_t)(size_t)ceilf(s->size[0] / s->smoothing_radius) + 2u;
+    sim->grid_h = (uint32_t)(size_t)ceilf(s->size[1] / s->smoothing_radius) + 2u;
+    const uint64_t cells64 = (uint64_t)sim->grid_w * sim->grid_h;
+    if (cells64 >= (1ull << 31)) { delete sim; return invalid("fluid_sim_create: grid has too many cells for u32 keys"); }
+    sim->num_cells = (uint32_t)cells64;
+    sim->sort_passes = (bits_for(sim->num_cells - 1) + RADIX_BITS - 1) / RADIX_BITS;
+    int rc = FLUID_OK;
+    auto fail = [&](int code) { fluid_sim_destroy(reinterpret_cast<FluidSim*>(sim)); return code; };
+    if (cudaStreamCreateWithFlags(&sim->stream, cudaStreamNonBlocking) != cudaSuccess) return fail(cuda_fail(cudaGetLastError(), "cudaStreamCreate", __FILE__, __LINE__));
+    if ((rc = sim->alloc(sim->n)) != FLUID_OK) return fail(rc);
+    const size_t tex_len = (size_t)s->texture_size[0] * s->texture_size[1];
+    if (cudaMalloc(&sim->start_indices, (size_t)sim->num_cells * 4) != cudaSuccess ||
+        cudaMalloc(&sim->cell_lb, ((size_t)sim->num_cells + 1) * 4) != cudaSuccess ||
+        cudaMalloc(&sim->quirk, 16) != cudaSuccess || cudaMalloc(&sim->d_frame_time, 4) != cudaSuccess ||
+        cudaMalloc(&sim->force_field, tex_len * 8) != cudaSuccess)
+        return fail(cuda_fail(cudaGetLastError(), "cudaMalloc(tables)", __FILE__, __LINE__));
+    // zero-initialised like wgpu's un-mapped buffers (src/simulation.rs:204-218)
+    cudaMemsetAsync(sim->start_indices, 0, (size_t)sim->num_cells * 4, sim->stream);
+    cudaMemsetAsync(sim->cell_lb, 0, ((size_t)sim->num_cells + 1) * 4, sim->stream);
+    cudaMemsetAsync(sim->quirk, 0, 16, sim->stream);
+    cudaMemsetAsync(sim->d_frame_time, 0, 4, sim->stream);
+    cudaMemsetAsync(sim->force_field, 0, tex_len * 8, sim->stream);
+    cudaFuncSetAttribute(k_onesweep_pass<SORT_ITEMS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SORT_TILE * 8);
+    cudaFuncSetAttribute(k_onesweep_pass<SORT_ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SORT_TILE * 8);
+
+    // init lattice, src/simulation.rs:147-163 (host arithmetic, uploaded once like create_buffer_init :168-172)
+    {
+        const uint32_t n = sim->n;
+        std::vector<FluidParticle> host(n);
+        const float ppr = sqrtf((float)n);
+        const float ppc = ((float)n - 1.0f) / ppr + 1.0f;
+        const size_t ppr_u = (size_t)ppr;
+        for (uint32_t i = 0; i < n; i++) {
+            const size_t xi = (size_t)i % ppr_u;
+            const float x = ((float)xi - ppr * 0.5f + 0.5f) * s->particle_spacing;
+            const float y = (floorf((float)i / ppr) - ppc * 0.5f + 0.5f) * s->particle_spacing;
+            FluidParticle q;
+            memset(&q, 0, sizeof q);
+            q.position[0] = x; q.position[1] = y;
+            q.predicted_position[0] = x; q.predicted_position[1] = y;
+            host[i] = q;
+        }
+        if ((rc = fluid_sim_upload_particles(reinterpret_cast<FluidSim*>(sim), host.data())) != FLUID_OK) return fail(rc);
+    }
+    FluidTickSettings zero_tick;
+    memset(&zero_tick, 0, sizeof zero_tick);
+    sim->make_uniform(zero_tick, 0, &sim->last_uniform);
+    if (cudaStreamSynchronize(sim->stream) != cudaSuccess) return fail(cuda_fail(cudaGetLastError(), "sync after create", __FILE__, __LINE__));
+    *out = reinterpret_cast<FluidSim*>(sim);
+    return FLUID_OK;
+}
+
+void fluid_sim_destroy(FluidSim* h) {
+    if (!h) return;
+    Sim* s = reinterpret_cast<Sim*>(h);
+    cudaSetDevice(s->device);
+    if (s->stream) cudaStreamSynchronize(s->stream);
+    void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
+                    s->idx_b, s->sort_scratch, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
+                    s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b};
+    for (void* b : bufs) if (b) cudaFree(b);
+    for (auto& e : s->mark_events) if (e) cudaEventDestroy(e);
+    if (s->stream) cudaStreamDestroy(s->stream);
+    cudaGetLastError();
+    delete s;
+}
+
+#define SIM_OR_FAIL(h)                                                   \
+    if (!(h)) return invalid("null FluidSim handle");                    \
+    Sim* s = reinterpret_cast<Sim*>(h);                                  \
+    FLUID_CUDA(cudaSetDevice(s->device));
+
+int fluid_sim_tick(FluidSim* h, const FluidTickSettings* t) {
+    SIM_OR_FAIL(h);
+    if (!t) return invalid("fluid_sim_tick: null settings");
+    return s->enqueue_tick(*t, false);
+}
+int fluid_sim_tick_n(FluidSim* h, const FluidTickSettings* t, uint32_t count) {
+    SIM_OR_FAIL(h);
+    if (!t) return invalid("fluid_sim_tick_n: null settings");
+    for (uint32_t k = 0; k < count; k++) {
+        int rc = s->enqueue_tick(*t, false);
+        if (rc != FLUID_OK) return rc;
+    }
+    return FLUID_OK;
+}
+int fluid_sim_tick_hash_sort_only(FluidSim* h, const FluidTickSettings* t) {
+    SIM_OR_FAIL(h);
+    if (!t) return invalid("fluid_sim_tick_hash_sort_only: null settings");
+    return s->enqueue_tick(*t, true);
+}
+int fluid_sim_sync(FluidSim* h) {
+    SIM_OR_FAIL(h);
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+uint32_t fluid_sim_tick_count(const FluidSim* h) { return h ? reinterpret_cast<const Sim*>(h)->tick : 0; }
+int fluid_sim_set_tick_count(FluidSim* h, uint32_t tick) {
+    SIM_OR_FAIL(h);
+    s->tick = tick;
+    FLUID_CUDA(cudaMemcpyAsync(s->d_frame_time, &s->tick, 4, cudaMemcpyHostToDevice, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+
+uint32_t fluid_sim_particle_count(const FluidSim* h) { return h ? reinterpret_cast<const Sim*>(h)->n : 0; }
+uint32_t fluid_sim_grid_w(const FluidSim* h) { return h ? reinterpret_cast<const Sim*>(h)->grid_w : 0; }
+uint32_t fluid_sim_grid_h(const FluidSim* h) { return h ? reinterpret_cast<const Sim*>(h)->grid_h : 0; }
+
+static int ensure_stage(Sim* s) {
+    if (!s->aos_stage) FLUID_CUDA(cudaMalloc(&s->aos_stage, ((size_t)s->capacity + 64) * sizeof(FluidParticle)));
+    return FLUID_OK;
+}
+
+int fluid_sim_download_particles(FluidSim* h, FluidParticle* dst) {
+    SIM_OR_FAIL(h);
+    if (!dst) return invalid("fluid_sim_download_particles: null destination");
+    int rc = ensure_stage(s);
+    if (rc != FLUID_OK) return rc;
+    k_soa_to_aos<<<(s->n + 255) / 256, 256, 0, s->stream>>>(s->aos_stage, s->n, s->pos_a, s->pred_s, s->vel_a, s->rho, s->keys_sorted);
+    s->launches++;
+    FLUID_CUDA(cudaMemcpyAsync(dst, s->aos_stage, (size_t)s->n * sizeof(FluidParticle), cudaMemcpyDeviceToHost, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+int fluid_sim_upload_particles(FluidSim* h, const FluidParticle* src) {
+    SIM_OR_FAIL(h);
+    if (!src) return invalid("fluid_sim_upload_particles: null source");
+    int rc = ensure_stage(s);
+    if (rc != FLUID_OK) return rc;
+    FLUID_CUDA(cudaMemcpyAsync(s->aos_stage, src, (size_t)s->n * sizeof(FluidParticle), cudaMemcpyHostToDevice, s->stream));
+    k_aos_to_soa<<<(s->n + 255) / 256, 256, 0, s->stream>>>(s->aos_stage, s->n, s->pos_a, s->pred_s, s->vel_a, s->rho, s->keys_sorted);
+    s->launches++;
+    FLUID_CUDA(cudaGetLastError());
+    // the source buffer may be pageable: the copy above is then already complete on return; for pinned
+    // memory the caller must not modify `src` before the next fluid_sim_sync / download.
+    return FLUID_OK;
+}
+int fluid_sim_download_start_indices(FluidSim* h, uint32_t* dst) {
+    SIM_OR_FAIL(h);
+    if (!dst) return invalid("null destination");
+    FLUID_CUDA(cudaMemcpyAsync(dst, s->start_indices, (size_t)s->num_cells * 4, cudaMemcpyDeviceToHost, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+int fluid_sim_upload_start_indices(FluidSim* h, const uint32_t* src) {
+    SIM_OR_FAIL(h);
+    if (!src) return invalid("null source");
+    FLUID_CUDA(cudaMemcpyAsync(s->start_indices, src, (size_t)s->num_cells * 4, cudaMemcpyHostToDevice, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+int fluid_sim_upload_force_field(FluidSim* h, const float* xy) {
+    SIM_OR_FAIL(h);
+    if (!xy) return invalid("null source");
+    const size_t len = (size_t)s->settings.texture_size[0] * s->settings.texture_size[1];
+    FLUID_CUDA(cudaMemcpyAsync(s->force_field, xy, len * 8, cudaMemcpyHostToDevice, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+int fluid_sim_download_force_field(FluidSim* h, float* xy) {
+    SIM_OR_FAIL(h);
+    if (!xy) return invalid("null destination");
+    const size_t len = (size_t)s->settings.texture_size[0] * s->settings.texture_size[1];
+    FLUID_CUDA(cudaMemcpyAsync(xy, s->force_field, len * 8, cudaMemcpyDeviceToHost, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+int fluid_sim_get_uniform(const FluidSim* h, FluidSimUniform* out) {
+    if (!h || !out) return invalid("null argument");
+    *out = reinterpret_cast<const Sim*>(h)->last_uniform;
+    return FLUID_OK;
+}
+int fluid_sim_download_unsorted_keys(FluidSim* h, uint32_t* dst) {
+    SIM_OR_FAIL(h);
+    if (!dst) return invalid("null destination");
+    FLUID_CUDA(cudaMemcpyAsync(dst, s->keys_u, (size_t)s->n * 4, cudaMemcpyDeviceToHost, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+int fluid_sim_download_permutation(FluidSim* h, uint32_t* dst) {
+    SIM_OR_FAIL(h);
+    if (!dst) return invalid("null destination");
+    if (!s->idx_sorted) return invalid("fluid_sim_download_permutation: no tick has run yet");
+    FLUID_CUDA(cudaMemcpyAsync(dst, s->idx_sorted, (size_t)s->n * 4, cudaMemcpyDeviceToHost, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+int fluid_sim_enable_debug_force(FluidSim* h, int enable) {
+    SIM_OR_FAIL(h);
+    if (enable && !s->dbg_accel) {
+        FLUID_CUDA(cudaMalloc(&s->dbg_accel, ((size_t)s->capacity + 64) * 8));
+        FLUID_CUDA(cudaMalloc(&s->dbg_abs, ((size_t)s->capacity + 64) * 8));
+    }
+    s->debug_force = enable != 0;
+    return FLUID_OK;
+}
+int fluid_sim_download_debug_force(FluidSim* h, float* accel_xy, float* abs_xy) {
+    SIM_OR_FAIL(h);
+    if (!s->dbg_accel) return invalid("debug force was never enabled");
+    if (accel_xy) FLUID_CUDA(cudaMemcpyAsync(accel_xy, s->dbg_accel, (size_t)s->n * 8, cudaMemcpyDeviceToHost, s->stream));
+    if (abs_xy) FLUID_CUDA(cudaMemcpyAsync(abs_xy, s->dbg_abs, (size_t)s->n * 8, cudaMemcpyDeviceToHost, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+int fluid_sim_device_view(FluidSim* h, FluidSimDeviceView* out) {
+    SIM_OR_FAIL(h);
+    if (!out) return invalid("null argument");
+    out->particle_count = s->n; out->capacity = s->capacity;
+    out->position = s->pos_a; out->predicted_position = s->pred_s; out->velocity = s->vel_a;
+    out->density = s->rho; out->grid = s->keys_sorted;
+    out->start_indices = s->start_indices; out->cell_lower_bound = s->cell_lb; out->force_field = s->force_field;
+    return FLUID_OK;
+}
+void* fluid_sim_stream(FluidSim* h) { return h ? (void*)reinterpret_cast<Sim*>(h)->stream : nullptr; }
+
+int fluid_sim_enable_timing(FluidSim* h, int enable) {
+    SIM_OR_FAIL(h);
+    s->timing = enable != 0;
+    s->n_marks = 0;
+    return FLUID_OK;
+}
+int fluid_sim_last_timing(FluidSim* h, const char** names, float* ms, int cap) {
+    SIM_OR_FAIL(h);
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    int out = 0;
+    for (int k = 1; k < s->n_marks && out < cap; k++, out++) {
+        float t = 0.f;
+        FLUID_CUDA(cudaEventElapsedTime(&t, s->mark_events[k - 1], s->mark_events[k]));
+        if (names) names[out] = s->mark_names[k];
+        if (ms) ms[out] = t;
+    }
+    return out;
+}
+uint64_t fluid_sim_launch_count(const FluidSim* h) { return h ? reinterpret_cast<const Sim*>(h)->launches : 0; }
+
+int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
+    SIM_OR_FAIL(h);
+    if (capacity <= s->capacity) return FLUID_OK;
+    // contents are preserved through a host-free device round trip of the live arrays
+    const uint32_t n = s->n;
+    float2 *pa = nullptr, *va = nullptr, *pr = nullptr; float* rh = nullptr; uint32_t* ks = nullptr;
+    FLUID_CUDA(cudaMalloc(&pa, (size_t)n * 8)); FLUID_CUDA(cudaMalloc(&va, (size_t)n * 8)); FLUID_CUDA(cudaMalloc(&pr, (size_t)n * 8));
+    FLUID_CUDA(cudaMalloc(&rh, (size_t)n * 4)); FLUID_CUDA(cudaMalloc(&ks, (size_t)n * 4));
+    FLUID_CUDA(cudaMemcpyAsync(pa, s->pos_a, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
+    FLUID_CUDA(cudaMemcpyAsync(va, s->vel_a, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
+    FLUID_CUDA(cudaMemcpyAsync(pr, s->pred_s, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
+    FLUID_CUDA(cudaMemcpyAsync(rh, s->rho, (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream));
+    FLUID_CUDA(cudaMemcpyAsync(ks, s->keys_sorted, (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    const bool dbg = s->debug_force;
+    int rc = s->alloc(capacity);
+    if (rc != FLUID_OK) return rc;
+    FLUID_CUDA(cudaMemcpyAsync(s->pos_a, pa, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
+    FLUID_CUDA(cudaMemcpyAsync(s->vel_a, va, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
+    FLUID_CUDA(cudaMemcpyAsync(s->pred_s, pr, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
+    FLUID_CUDA(cudaMemcpyAsync(s->rho, rh, (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream));
+    FLUID_CUDA(cudaMemcpyAsync(s->keys_sorted, ks, (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    cudaFree(pa); cudaFree(va); cudaFree(pr); cudaFree(rh); cudaFree(ks);
+    s->idx_sorted = nullptr;
+    if (dbg) return fluid_sim_enable_debug_force(h, 1);
+    return FLUID_OK;
+}
+int fluid_sim_set_particle_count(FluidSim* h, uint32_t n) {
+    SIM_OR_FAIL(h);
+    if (n < 2 || n > s->capacity) return invalid("fluid_sim_set_particle_count: need 2 <= n <= capacity");
+    s->n = n;
+    return FLUID_OK;
+}
+
+}  // extern "C"

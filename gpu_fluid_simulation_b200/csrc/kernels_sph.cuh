@@ -1,0 +1,379 @@
+// kernels_sph.cuh — the two neighbour passes: density (K5) and force + integrate (K6).
+//
+// Reference: calculate_density (compute.wgsl:59-74 -> funcs.wgsl:157-203) and move_particle
+// (compute.wgsl:79-157 -> calculate_pressure_force :160-235, calculate_viscosity_force :238-299).
+//
+// B200 shape. Keys are row-major (funcs.wgsl:216-218) and the particle arrays are in key order, so
+// the 3 cells (x-1, x, x+1) of one grid row are ONE contiguous span of the sorted arrays, and a
+// CTA that owns 256 consecutive sorted particles needs, for each of the three grid rows around it,
+// one contiguous span too. The CTA stages those spans (predicted position; plus velocity and density
+// for the force pass) in shared memory with 1-D TMA bulk copies (cp.async.bulk -> mbarrier), then
+// each thread walks its own three sub-spans out of shared memory in ascending index order — which is
+// exactly the reference's visiting order (rows y-1, y, y+1; cells x-1, x, x+1; ascending index in a
+// cell), so every fp32 sum is accumulated in the reference's order.
+//   * density walks 3x3 cells, not the reference's 7x7: the outer rings only ever add +0.0
+//     (cell size == h); tests compare against the 7x7 oracle.
+//   * pressure and viscosity are accumulated in ONE walk with separate accumulators: same order, same
+//     bits as the reference's two walks, half the traffic.
+//   * move_particle reads neighbour velocity from the sorted snapshot and writes the new state to a
+//     different buffer: Jacobi semantics by construction (the reference has a data race here,
+//     SURVEY.md §3.3).
+// A CTA whose particles straddle grid rows and whose neighbourhood does not fit the staging buffer
+// (a row boundary inside a long row) falls back to walking the same spans straight from global/L2.
+#pragma once
+#include "common.cuh"
+
+namespace fluid {
+
+constexpr int SPH_THREADS = 256;
+constexpr int SPH_CAP = 1536;  // staged particles per CTA (3 row spans of ~256+2 cells, rounded)
+
+struct SpanPlan {
+    // per grid row r (0..2 = y-1, y, y+1 in the single-row case): global index of the first staged
+    // particle minus its offset in the staging buffer, so smem index = global index - base[r]
+    int base[3];
+    int staged;  // 1: spans are in shared memory; 0: walk global memory
+};
+
+// thread-0 planning: which global index intervals does this CTA need, do they fit, issue the copies.
+// arrays[k] / smem[k] / elem_bytes[k]: the SoA streams to stage (1 for density, 3 for force).
+template <int NARR>
+__device__ __forceinline__ void plan_and_stage(const DevParams& p, uint32_t i0, uint32_t i1,
+                                               const uint32_t* __restrict__ keys, const uint32_t* __restrict__ lb,
+                                               const void* const (&arrays)[NARR], void* const (&smem)[NARR],
+                                               const uint32_t (&elem_bytes)[NARR], uint64_t* bar, SpanPlan* plan) {
+    const uint32_t kf = min(__ldg(keys + i0), p.num_cells - 1u), kl = min(__ldg(keys + i1 - 1u), p.num_cells - 1u);
+    const uint32_t yf = kf / p.grid_w, xa = kf - yf * p.grid_w;
+    const uint32_t yl = kl / p.grid_w, xb = kl - yl * p.grid_w;
+    uint32_t lo[3], hi[3];
+    int nint;
+    if (yf == yl) {
+        nint = 3;
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            const uint32_t row = yf + (uint32_t)r - 1u;  // wraps for yf == 0 -> fails the range test
+            if (row < p.grid_h) {
+                const uint32_t ca = row * p.grid_w + (xa > 0u ? xa - 1u : 0u);
+                const uint32_t cb = row * p.grid_w + min(xb + 2u, p.grid_w);
+                lo[r] = __ldg(lb + ca);
+                hi[r] = __ldg(lb + cb);
+            } else {
+                lo[r] = 0; hi[r] = 0;
+            }
+        }
+    } else {
+        nint = 1;
+        const uint32_t ca = yf > 0u ? (yf - 1u) * p.grid_w + (xa > 0u ? xa - 1u : 0u) : 0u;
+        const uint32_t cb = (yl + 1u < p.grid_h) ? (yl + 1u) * p.grid_w + min(xb + 2u, p.grid_w) : p.num_cells;
+        lo[0] = __ldg(lb + ca);
+        hi[0] = __ldg(lb + cb);
+        lo[1] = lo[2] = hi[1] = hi[2] = 0;
+    }
+    // 16-byte granularity for every stream: round to multiples of 4 particles
+    uint32_t total = 0, off[3];
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        lo[r] &= ~3u;
+        hi[r] = (hi[r] + 3u) & ~3u;
+        if (hi[r] < lo[r]) hi[r] = lo[r];
+        off[r] = total;
+        total += hi[r] - lo[r];
+    }
+    if (total > (uint32_t)SPH_CAP) {
+        plan->staged = 0;
+        plan->base[0] = plan->base[1] = plan->base[2] = 0;
+        return;
+    }
+    plan->staged = 1;
+    if (nint == 3) {
+#pragma unroll
+        for (int r = 0; r < 3; r++) plan->base[r] = (int)lo[r] - (int)off[r];
+    } else {
+        plan->base[0] = plan->base[1] = plan->base[2] = (int)lo[0];
+    }
+    uint32_t bytes = 0;
+#pragma unroll
+    for (int k = 0; k < NARR; k++) bytes += total * elem_bytes[k];
+    if (bytes == 0) { mbar_arrive_expect_tx(bar, 0); return; }
+    mbar_arrive_expect_tx(bar, bytes);
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const uint32_t len = hi[r] - lo[r];
+        if (len == 0) continue;
+#pragma unroll
+        for (int k = 0; k < NARR; k++) {
+            bulk_g2s(reinterpret_cast<char*>(smem[k]) + (size_t)off[r] * elem_bytes[k],
+                     reinterpret_cast<const char*>(arrays[k]) + (size_t)lo[r] * elem_bytes[k], len * elem_bytes[k], bar);
+        }
+    }
+}
+
+// this thread's three spans [a[r], b[r]) in global sorted-index space
+__device__ __forceinline__ void thread_spans(const DevParams& p, uint32_t key, const uint32_t* __restrict__ lb,
+                                             uint32_t c0, uint32_t s_stale, uint32_t (&a)[3], uint32_t (&b)[3]) {
+    const uint32_t k = min(key, p.num_cells - 1u);
+    const uint32_t cy = k / p.grid_w, cx = k - cy * p.grid_w;
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const uint32_t row = cy + (uint32_t)r - 1u;
+        a[r] = 0; b[r] = 0;
+        if (row < p.grid_h) {  // [survey-pinned] rows outside the grid are empty
+            const uint32_t ca = row * p.grid_w + (cx > 0u ? cx - 1u : 0u);
+            const uint32_t cb = row * p.grid_w + min(cx + 2u, p.grid_w);  // column grid_w is the next row's empty column 0
+            uint32_t lo = __ldg(lb + ca), hi = __ldg(lb + cb);
+            // lowest occupied cell: the reference walks it from its stale start_indices entry
+            if (ca <= c0 && c0 < cb) lo = min(max(lo, s_stale), hi);
+            a[r] = lo; b[r] = hi;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5 density
+// ------------------------------------------------------------------------------------------------
+template <bool STAGED>
+__device__ __forceinline__ float density_walk(const DevParams& p, const float2* __restrict__ src, const int (&base)[3],
+                                              const uint32_t (&a)[3], const uint32_t (&b)[3], float px, float py) {
+    float density = 0.0f;
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const float2* s = src - (STAGED ? base[r] : 0);
+        for (uint32_t j = a[r]; j < b[r]; j++) {
+            const float2 q = s[j];
+            const float dx = fsub(q.x, px), dy = fsub(q.y, py);
+            const float r2 = fadd(fmul(dx, dx), fmul(dy, dy));
+            if (r2 <= p.h2) {  // funcs.wgsl:74 (r2 > h2 -> 0, and +0 does not change the sum)
+                const float diff = fsub(p.h2, r2);
+                const float k = fmul(fmul(fmul(p.poly6_norm, diff), diff), diff);
+                density = fadd(density, fmul(p.mass, k));
+            }
+        }
+    }
+    return density;
+}
+
+__global__ void __launch_bounds__(SPH_THREADS)
+k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* __restrict__ keys,
+          const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk, float* __restrict__ rho) {
+    __shared__ __align__(128) float2 s_pred[SPH_CAP];
+    __shared__ uint64_t s_bar;
+    __shared__ SpanPlan s_plan;
+    const uint32_t i0 = blockIdx.x * SPH_THREADS;
+    const uint32_t i1 = min(i0 + SPH_THREADS, p.n);
+    if (threadIdx.x == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_fence_init();
+        const void* const arrays[1] = {pred_s};
+        void* const smem[1] = {s_pred};
+        const uint32_t eb[1] = {8u};
+        plan_and_stage<1>(p, i0, i1, keys, lb, arrays, smem, eb, &s_bar, &s_plan);
+    }
+    const uint32_t i = i0 + threadIdx.x;
+    const bool valid = i < p.n;
+    uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
+    float2 me = make_float2(0.f, 0.f);
+    if (valid) {
+        thread_spans(p, __ldg(keys + i), lb, __ldg(quirk), __ldg(quirk + 1), a, b);
+        me = __ldg(pred_s + i);
+    }
+    __syncthreads();
+    const int staged = s_plan.staged;
+    float d;
+    if (staged) {
+        mbar_wait(&s_bar, 0);
+        const int base[3] = {s_plan.base[0], s_plan.base[1], s_plan.base[2]};
+        d = density_walk<true>(p, s_pred, base, a, b, me.x, me.y);
+    } else {
+        const int base[3] = {0, 0, 0};
+        d = density_walk<false>(p, pred_s, base, a, b, me.x, me.y);
+    }
+    // funcs.wgsl:202 max(density, EPSILON); compute.wgsl:70 max(.., 0.1)
+    if (valid) rho[i] = fmaxf(fmaxf(d, 1.19209290e-07f), 0.1f);
+}
+
+// ------------------------------------------------------------------------------------------------
+// K6 force + integrate
+// ------------------------------------------------------------------------------------------------
+// funcs.wgsl:129-142
+__device__ __forceinline__ float rand_f32(uint32_t& s) {
+    uint32_t x = s;
+    x ^= x << 13; x ^= x >> 17; x ^= x << 5;
+    s = x;
+    return fmul(__uint2float_rn(x), 2.3283064365386962890625e-10f);  // exact: / 4294967296.0
+}
+// funcs.wgsl:112-123
+__device__ __forceinline__ float viscosity_kernel(const DevParams& p, float r) {
+    if (r <= p.h) {
+        if (r == 0.0f) return p.visc_k;
+        const float A = fdiv(-fmul(fmul(r, r), r), p.two_h3);
+        const float B = fdiv(fmul(r, r), p.h2);
+        const float C = fdiv(p.h, fmul(2.0f, r));
+        return fmul(p.visc_k, fsub(fadd(fadd(A, B), C), 1.0f));
+    }
+    return 0.0f;
+}
+
+struct ForceAcc {
+    float px, py;  // pressure sum
+    float vx, vy;  // viscosity sum (before * viscosity_coefficient)
+    float ax, ay;  // sum of |terms| (debug only)
+};
+
+template <bool STAGED, bool DEBUG>
+__device__ __forceinline__ void force_walk(const DevParams& p, const float2* __restrict__ pred, const float2* __restrict__ vel,
+                                           const float* __restrict__ rho, const int (&base)[3], const uint32_t (&a)[3],
+                                           const uint32_t (&b)[3], uint32_t self, float px, float py, float vx, float vy,
+                                           float pressure, uint32_t& rand_seed, ForceAcc& acc) {
+#pragma unroll
+    for (int r = 0; r < 3; r++) {
+        const int bs = STAGED ? base[r] : 0;
+        const float2* sp = pred - bs;
+        const float2* sv = vel - bs;
+        const float* sr = rho - bs;
+        for (uint32_t j = a[r]; j < b[r]; j++) {
+            if (j == self) continue;  // compute.wgsl:195
+            const float2 q = sp[j];
+            const float dx = fsub(q.x, px), dy = fsub(q.y, py);
+            const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
+            if (sq > p.h2) continue;  // compute.wgsl:202 (sqr_radius == h*h)
+            const float dst = fsqrt(sq);
+            const float nd = sr[j];
+            const float2 nv = sv[j];
+            float dirx, diry;
+            if (dst == 0.0f) {  // compute.wgsl:211-212
+                const float rx = rand_f32(rand_seed);
+                const float ry = rand_f32(rand_seed);
+                const float len = fsqrt(fadd(fmul(rx, rx), fmul(ry, ry)));
+                dirx = fdiv(rx, len); diry = fdiv(ry, len);
+            } else {
+                dirx = fdiv(dx, dst); diry = fdiv(dy, dst);
+            }
+            const float np = fmul(p.pressure_constant, fsub(nd, p.rest_density));
+            const float k = (dst <= p.h) ? fmul(-fsub(p.h, dst), p.spiky) : 0.0f;  // funcs.wgsl:101-109
+            const float shared_p = fmul(fadd(pressure, np), 0.5f);
+            const float tx = fdiv(fmul(fmul(dirx, k), shared_p), nd);
+            const float ty = fdiv(fmul(fmul(diry, k), shared_p), nd);
+            acc.px = fadd(acc.px, tx);
+            acc.py = fadd(acc.py, ty);
+            const float kv = viscosity_kernel(p, dst);
+            const float ux = fmul(fdiv(fsub(nv.x, vx), nd), kv);  // compute.wgsl:288
+            const float uy = fmul(fdiv(fsub(nv.y, vy), nd), kv);
+            acc.vx = fadd(acc.vx, ux);
+            acc.vy = fadd(acc.vy, uy);
+            if (DEBUG) {
+                acc.ax += fabsf(tx) + fabsf(ux) * p.visc_coef;
+                acc.ay += fabsf(ty) + fabsf(uy) * p.visc_coef;
+            }
+        }
+    }
+}
+
+template <bool DEBUG>
+__global__ void __launch_bounds__(SPH_THREADS)
+k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const float2* __restrict__ pred_s,
+                  const float2* __restrict__ vel_s, const float* __restrict__ rho, const uint32_t* __restrict__ keys,
+                  const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk,
+                  const float2* __restrict__ force_field, const uint32_t* __restrict__ frame_time,
+                  float2* __restrict__ pos_out, float2* __restrict__ vel_out, float2* __restrict__ dbg_accel,
+                  float2* __restrict__ dbg_abs) {
+    __shared__ __align__(128) float2 s_pred[SPH_CAP];
+    __shared__ __align__(128) float2 s_vel[SPH_CAP];
+    __shared__ __align__(128) float s_rho[SPH_CAP];
+    __shared__ uint64_t s_bar;
+    __shared__ SpanPlan s_plan;
+    const uint32_t i0 = blockIdx.x * SPH_THREADS;
+    const uint32_t i1 = min(i0 + SPH_THREADS, p.n);
+    if (threadIdx.x == 0) {
+        mbar_init(&s_bar, 1);
+        mbar_fence_init();
+        const void* const arrays[3] = {pred_s, vel_s, rho};
+        void* const smem[3] = {s_pred, s_vel, s_rho};
+        const uint32_t eb[3] = {8u, 8u, 4u};
+        plan_and_stage<3>(p, i0, i1, keys, lb, arrays, smem, eb, &s_bar, &s_plan);
+    }
+    const uint32_t i = i0 + threadIdx.x;
+    const bool valid = i < p.n;
+    uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
+    float2 pos = make_float2(0.f, 0.f), pred = pos, vel = pos;
+    float dens = 1.0f;
+    if (valid) {
+        thread_spans(p, __ldg(keys + i), lb, __ldg(quirk), __ldg(quirk + 1), a, b);
+        pos = __ldg(pos_s + i);
+        pred = __ldg(pred_s + i);
+        vel = __ldg(vel_s + i);
+        dens = __ldg(rho + i);
+    }
+    const uint32_t ft = __ldg(frame_time);
+    uint32_t rand_seed = i * 12u + ft * 69u;  // compute.wgsl:161
+    const float pressure = fmul(p.pressure_constant, fsub(dens, p.rest_density));
+    ForceAcc acc = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    __syncthreads();
+    if (s_plan.staged) {
+        mbar_wait(&s_bar, 0);
+        const int base[3] = {s_plan.base[0], s_plan.base[1], s_plan.base[2]};
+        force_walk<true, DEBUG>(p, s_pred, s_vel, s_rho, base, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
+    } else {
+        const int base[3] = {0, 0, 0};
+        force_walk<false, DEBUG>(p, pred_s, vel_s, rho, base, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
+    }
+    if (!valid) return;
+
+    // compute.wgsl:90-96
+    const float fvx = fmul(acc.vx, p.visc_coef), fvy = fmul(acc.vy, p.visc_coef);
+    const float ax = fadd(acc.px, fvx), ay = fadd(acc.py, fvy);
+    if (DEBUG) {
+        dbg_accel[i] = make_float2(ax, ay);
+        dbg_abs[i] = make_float2(acc.ax, acc.ay);
+    }
+    float vx = fadd(vel.x, fmul(fdiv(ax, dens), p.dt));
+    float vy = fadd(vel.y, fmul(fdiv(ay, dens), p.dt));
+    vx = fadd(vx, p.gravity_dt_x);
+    vy = fadd(vy, p.gravity_dt_y);
+    // compute.wgsl:99-108 mouse force
+    if (p.mouse_state != 0) {
+        const float dx = fsub(p.mouse_x, pred.x), dy = fsub(p.mouse_y, pred.y);
+        const float dist = fsqrt(fadd(fmul(dx, dx), fmul(dy, dy)));
+        if (dist <= p.mouse_radius) {
+            const float dirx = fdiv(fdiv(dx, dist), dist), diry = fdiv(fdiv(dy, dist), dist);
+            const float ratio = fdiv(dist, p.mouse_radius);
+            vx = fadd(vx, fmul(fmul(fmul(dirx, p.mouse_power), p.mouse_state_f), ratio));
+            vy = fadd(vy, fmul(fmul(fmul(diry, p.mouse_power), p.mouse_state_f), ratio));
+        }
+    }
+    // compute.wgsl:113-116 NaN guard
+    if (!(vx == vx && vy == vy)) { vx = 0.0f; vy = 0.0f; }
+    // compute.wgsl:118-122 speed clamp
+    const float speed = fsqrt(fadd(fmul(vx, vx), fmul(vy, vy)));
+    if (speed > 500.0f) {
+        vx = fmul(fdiv(vx, speed), 500.0f);
+        vy = fmul(fdiv(vy, speed), 500.0f);
+    }
+    float nx = fadd(pos.x, fmul(vx, p.dt));
+    float ny = fadd(pos.y, fmul(vy, p.dt));
+    // compute.wgsl:127-140 force-field push-out (texel looked up at the PREDICTED position)
+    {
+        const float uvx = fadd(fmul(fdiv(pred.x, p.bounds_x), 1.0f), 0.5f);
+        const float uvy = fadd(fmul(fdiv(pred.y, p.bounds_y), 1.0f), 0.5f);
+        const uint32_t tx = f2u(fmul(uvx, p.tex_w)), ty = f2u(fmul(uvy, p.tex_h));
+        uint32_t tidx = ty * p.tex_wu + tx;
+        if (tidx >= p.tex_len) tidx = p.tex_len - 1u;  // [survey-pinned] out-of-range texel -> last texel
+        const float2 f = __ldg(force_field + tidx);
+        if (f.x != 0.0f || f.y != 0.0f) {
+            const float fwx = fmul(f.x, p.p2w_x), fwy = fmul(f.y, p.p2w_y);
+            const float len = fsqrt(fadd(fmul(f.x, f.x), fmul(f.y, f.y)));
+            const float nnx = fdiv(f.x, len), nny = fdiv(f.y, len);
+            nx = fadd(nx, fwx);
+            ny = fadd(ny, fwy);
+            const float vn = fadd(fmul(vx, nnx), fmul(vy, nny));
+            vx = fsub(vx, fmul(fmul(p.one_minus_damping, vn), nnx));
+            vy = fsub(vy, fmul(fmul(p.one_minus_damping, vn), nny));
+        }
+    }
+    // compute.wgsl:143-153 walls
+    if (fabsf(nx) > p.half_x) { nx = fmul(p.half_x, fsign(nx)); vx = fmul(vx, p.neg_damping); }
+    if (fabsf(ny) > p.half_y) { ny = fmul(p.half_y, fsign(ny)); vy = fmul(vy, p.neg_damping); }
+    pos_out[i] = make_float2(nx, ny);
+    vel_out[i] = make_float2(vx, vy);
+}
+
+}  // namespace fluid

@@ -1,0 +1,60 @@
+// sim_internal.h — the state behind the opaque FluidSim handle.
+#pragma once
+#include "common.cuh"
+
+namespace fluid {
+
+constexpr int SORT_ITEMS = 16;                          // keys per thread per onesweep tile
+constexpr uint32_t SORT_TILE = SORT_THREADS * SORT_ITEMS;
+constexpr int MAX_MARKS = 16;
+
+struct Sim {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    FluidSimSettings settings{};
+    uint32_t n = 0, capacity = 0;
+    uint32_t grid_w = 0, grid_h = 0, num_cells = 0;
+    uint32_t sort_passes = 1;
+    uint32_t tick = 0;             // reference: pub tick (src/simulation.rs:12)
+    FluidSimUniform last_uniform{};
+
+    // particle store, structure of arrays. *_a: state between ticks (input of a tick, output of
+    // force+integrate); *_s: this tick's key-ordered snapshot the neighbour passes read.
+    float2 *pos_a = nullptr, *vel_a = nullptr;
+    float2 *pos_s = nullptr, *vel_s = nullptr, *pred_s = nullptr;
+    float* rho = nullptr;
+    uint32_t *keys_u = nullptr, *keys_b = nullptr, *keys_c = nullptr;  // unsorted keys, sort ping-pong
+    uint32_t *idx_a = nullptr, *idx_b = nullptr;
+    uint32_t *keys_sorted = nullptr, *idx_sorted = nullptr;            // aliases into the above
+    uint32_t* sort_scratch = nullptr;
+    size_t sort_scratch_words = 0;
+    uint32_t max_tiles = 0;
+
+    uint32_t* start_indices = nullptr;  // reference-compatible table (compute.wgsl:45-56), never cleared
+    uint32_t* cell_lb = nullptr;        // dense lower-bound table, num_cells + 1 entries
+    uint32_t* quirk = nullptr;          // [0] lowest occupied cell c0, [1] its stale start_indices entry
+    uint32_t* d_frame_time = nullptr;   // device copy of `tick`, bumped by the first kernel of a tick
+    float2* force_field = nullptr;      // reference `texture` (src/simulation.rs:213-218)
+
+    FluidParticle* aos_stage = nullptr;
+    float2 *dbg_accel = nullptr, *dbg_abs = nullptr;
+    bool debug_force = false;
+
+    uint32_t *jfa_a = nullptr, *jfa_b = nullptr;  // packed seed ping-pong for fluid_sim_jfa_from_particles
+    size_t jfa_pixels = 0;
+
+    bool timing = false;
+    int n_marks = 0;
+    cudaEvent_t mark_events[MAX_MARKS] = {};
+    const char* mark_names[MAX_MARKS] = {};
+    uint64_t launches = 0;
+
+    int alloc(uint32_t cap);
+    void make_uniform(const FluidTickSettings& t, uint32_t tick_value, FluidSimUniform* out) const;
+    DevParams make_params(const FluidSimUniform& u) const;
+    void mark(const char* name);
+    int enqueue_tick(const FluidTickSettings& t, bool hash_sort_only);
+};
+
+}  // namespace fluid

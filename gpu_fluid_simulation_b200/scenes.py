@@ -1,0 +1,65 @@
+"""Synthetic scenes of SURVEY.md §8(d): uniform box (U) and dam-break (D).
+
+Inputs are generated once on the host (splitmix64, fixed seeds) and handed identically to the oracle
+and to the CUDA library through upload_particles, so the PRNG is not part of parity.
+"""
+import numpy as np
+
+from ._lib import PARTICLE_DTYPE
+from .simulation import SimulationSettings, TickSettings
+
+SEED_JITTER = 0xF1D00001
+SEED_VEL = 0xF1D00002
+_M = (1 << 64) - 1
+
+
+def splitmix64(seed: int, count: int) -> np.ndarray:
+    """`count` uniform doubles in [0,1) from splitmix64 (vectorised: state_i = seed + (i+1)*golden)."""
+    with np.errstate(over="ignore"):
+        i = np.arange(1, count + 1, dtype=np.uint64)
+        z = np.uint64(seed & _M) + i * np.uint64(0x9E3779B97F4A7C15)
+        z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        z = z ^ (z >> np.uint64(31))
+    return (z >> np.uint64(11)).astype(np.float64) * (1.0 / (1 << 53))
+
+
+def _block(cols: int, rows: int, spacing: float, x0: float, y0: float, jitter: float, vel_amp: float):
+    n = cols * rows
+    ix = (np.arange(n, dtype=np.int64) % cols).astype(np.float64)
+    iy = (np.arange(n, dtype=np.int64) // cols).astype(np.float64)
+    r = splitmix64(SEED_JITTER, 2 * n)
+    px = x0 + (ix + 0.5) * spacing + (r[0::2] * 2.0 - 1.0) * jitter * spacing
+    py = y0 + (iy + 0.5) * spacing + (r[1::2] * 2.0 - 1.0) * jitter * spacing
+    p = np.zeros(n, dtype=PARTICLE_DTYPE)
+    p["position"][:, 0] = px.astype(np.float32)
+    p["position"][:, 1] = py.astype(np.float32)
+    if vel_amp != 0.0:
+        v = splitmix64(SEED_VEL, 2 * n)
+        p["velocity"][:, 0] = ((v[0::2] * 2.0 - 1.0) * vel_amp).astype(np.float32)
+        p["velocity"][:, 1] = ((v[1::2] * 2.0 - 1.0) * vel_amp).astype(np.float32)
+    p["predicted_position"] = p["position"]
+    return p
+
+
+def uniform_box(n_side: int, spacing=0.1, h=0.2, tex=(1024, 1024)):
+    """Scene U: n x n jittered lattice filling size = (n*s, n*s); vel uniform in [-1,1]^2."""
+    size = (n_side * spacing, n_side * spacing)
+    settings = SimulationSettings(particle_count=n_side * n_side, particle_spacing=spacing, smoothing_radius=h,
+                                  size=size, texture_size=tex)
+    p = _block(n_side, n_side, spacing, -size[0] / 2, -size[1] / 2, 0.25, 1.0)
+    return settings, TickSettings(), p
+
+
+def dam_break(cols: int, rows: int, spacing=0.1, h=0.2, tex=(1024, 1024)):
+    """Scene D: cols x rows jittered block against the left wall of a box 4x as wide; gravity (0, 9.8)."""
+    size = (cols * spacing * 4.0, rows * spacing)
+    settings = SimulationSettings(particle_count=cols * rows, particle_spacing=spacing, smoothing_radius=h,
+                                  size=size, texture_size=tex)
+    p = _block(cols, rows, spacing, -size[0] / 2, -size[1] / 2, 0.25, 0.0)
+    return settings, TickSettings(gravity=(0.0, 9.8)), p
+
+
+def assert_no_coincident(p: np.ndarray):
+    pos = np.ascontiguousarray(p["predicted_position"]).view(np.uint64).ravel()
+    assert np.unique(pos).size == pos.size, "scene contains coincident positions"

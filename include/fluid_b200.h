@@ -1,0 +1,231 @@
+/*
+ * fluid_b200.h — C ABI of libfluid_b200.so, the B200 (sm_100a) backend for the
+ * per-frame fluid step of rookieCookies/gpu-fluid-simulation.
+ *
+ * Every entry point replaces one piece of the reference's Rust `FluidSimulation`
+ * API (reference `src/simulation.rs`) or one host-side step the reference performs
+ * around it; the reference interface each one stands in for is cited beside it.
+ * Plain pointers and sizes only; no CUDA, torch or C++ types cross this boundary.
+ *
+ * Conventions
+ *   - every function returns FLUID_OK (0) or a negative FluidStatus;
+ *     fluid_last_error() gives the thread-local message of the last failure.
+ *   - a FluidSim handle owns all of its device memory and one CUDA stream; it is
+ *     NOT thread-safe (one caller thread at a time, like the reference, which only
+ *     touches FluidSimulation from the winit thread).
+ *   - the caller owns every host pointer it passes; none is retained past the call.
+ *   - there is no CPU fallback: without a usable CUDA device create() fails.
+ */
+#ifndef FLUID_B200_H
+#define FLUID_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FLUID_B200_ABI_VERSION 1
+
+typedef enum FluidStatus {
+    FLUID_OK = 0,
+    FLUID_ERR_INVALID_ARGUMENT = -1, /* null pointer, particle_count < 2, bad sizes */
+    FLUID_ERR_CUDA = -2,             /* a CUDA runtime call failed; see fluid_last_error */
+    FLUID_ERR_NO_DEVICE = -3,        /* no CUDA device / ordinal out of range */
+    FLUID_ERR_UNSUPPORTED = -4       /* e.g. image larger than the JFA seed encoding allows */
+} FluidStatus;
+
+/* reference: `ParticleInstance`, src/simulation.rs:126-135 (WGSL twin funcs.wgsl:1-8).
+ * 32 bytes, align 4. The particle buffer is physically in key order after a tick. */
+typedef struct FluidParticle {
+    float position[2];
+    float predicted_position[2];
+    float velocity[2];
+    float density;
+    uint32_t grid;
+} FluidParticle;
+
+/* reference: `SimulationUniform`, src/simulation.rs:53-90 (WGSL twin funcs.wgsl:17-51). 120 bytes. */
+typedef struct FluidSimUniform {
+    float delta;
+    uint32_t particle_count;
+    float sqr_radius;
+    uint32_t frame_time;
+    float gravity[2];
+    float bounds[2];
+    float mouse_pos[2];
+    float smoothing_radius;
+    float particle_mass;
+    float pressure_constant;
+    float rest_density;
+    float damping_factor;
+    float viscosity_coefficient;
+    float surface_tension_treshold;
+    float surface_tension_coefficient;
+    float poly6_kernel_volume;
+    float poly6_kernel_derivative;
+    float poly6_kernel_laplacian;
+    float spiky_kernel_derivative;
+    float viscosity_kernel;
+    int32_t mouse_state;
+    float mouse_force_radius;
+    float mouse_force_power;
+    uint32_t grid_w;
+    uint32_t grid_h;
+    float texture_size[2];
+} FluidSimUniform;
+
+/* reference: `SimulationSettings`, src/simulation.rs:95-104 (same field order). */
+typedef struct FluidSimSettings {
+    uint32_t particle_count;
+    float particle_spacing;
+    float smoothing_radius;
+    float size[2];
+    uint32_t texture_size[2];
+} FluidSimSettings;
+
+/* reference: `TickSettings`, src/simulation.rs:107-122 (same field order). */
+typedef struct FluidTickSettings {
+    float delta;
+    float gravity[2];
+    float mass;
+    float pressure_constant;
+    float rest_density;
+    float damping_factor;
+    float viscosity_coefficient;
+    float surface_tension_treshold;
+    float surface_tension_coefficient;
+    float mouse_force_radius;
+    float mouse_force_power;
+    float mouse_pos[2];
+    int32_t mouse_state;
+} FluidTickSettings;
+
+typedef struct FluidSim FluidSim; /* opaque */
+
+const char* fluid_last_error(void);
+int fluid_abi_version(void);
+/* number of CUDA devices visible; negative FluidStatus on failure. */
+int fluid_device_count(void);
+
+/* ---- construction / destruction ------------------------------------------------ */
+
+/* reference: `FluidSimulation::new(&Device, SimulationSettings)`, src/simulation.rs:139.
+ * Builds the init lattice of src/simulation.rs:147-163 bit for bit, zero-initialises
+ * start_indices (src/simulation.rs:204-209) and the force field (:213-218).
+ * particle_count < 2 is rejected (the reference panics at src/simulation.rs:323-324). */
+int fluid_sim_create(const FluidSimSettings* settings, int device_ordinal, FluidSim** out);
+/* reference: Drop of FluidSimulation (rebuilt on restart, src/renderer.rs:873-875). */
+void fluid_sim_destroy(FluidSim* sim);
+
+/* ---- stepping -------------------------------------------------------------------- */
+
+/* reference: `FluidSimulation::tick`, src/simulation.rs:459-539. Increments the tick
+ * counter first (:460), derives the uniform (:470-497) and enqueues the whole step
+ * (predict, key, sort, cell-start, density, force+integrate) on the handle's stream.
+ * Asynchronous, mirroring the reference's record-then-submit (src/main.rs:226). */
+int fluid_sim_tick(FluidSim* sim, const FluidTickSettings* tick);
+/* `n` consecutive ticks with the same settings (reference: the Running/Render loops,
+ * src/main.rs:137-147,199-201), replayed from a captured CUDA graph. */
+int fluid_sim_tick_n(FluidSim* sim, const FluidTickSettings* tick, uint32_t n);
+/* reference: `device.poll(Wait)`, src/main.rs:79. */
+int fluid_sim_sync(FluidSim* sim);
+/* reference: `pub tick: u32`, src/simulation.rs:12. */
+uint32_t fluid_sim_tick_count(const FluidSim* sim);
+int fluid_sim_set_tick_count(FluidSim* sim, uint32_t tick);
+
+/* BASELINE.json config 2: spatial hash + key sort + cell-start table only
+ * (reference passes K1..K4: compute.wgsl:8-56, sort.wgsl:27-51). Increments tick. */
+int fluid_sim_tick_hash_sort_only(FluidSim* sim, const FluidTickSettings* tick);
+
+/* ---- state exposure (headless stand-ins for the wgpu bind-group getters,
+ *      src/simulation.rs:542-564) ------------------------------------------------- */
+
+uint32_t fluid_sim_particle_count(const FluidSim* sim);
+uint32_t fluid_sim_grid_w(const FluidSim* sim);
+uint32_t fluid_sim_grid_h(const FluidSim* sim);
+
+/* binding 0 of simulation_bg: N x 32 B AoS, in the current (sorted) physical order. */
+int fluid_sim_download_particles(FluidSim* sim, FluidParticle* dst);
+int fluid_sim_upload_particles(FluidSim* sim, const FluidParticle* src);
+/* binding 1: grid_w*grid_h u32, reference semantics (never cleared, compute.wgsl:45-56). */
+int fluid_sim_download_start_indices(FluidSim* sim, uint32_t* dst);
+int fluid_sim_upload_start_indices(FluidSim* sim, const uint32_t* src);
+/* binding 2: reference `queue.write_buffer(force_field_texture(), ..)`, src/renderer.rs:498-502.
+ * tex_w*tex_h (x,y) float pairs. */
+int fluid_sim_upload_force_field(FluidSim* sim, const float* xy);
+int fluid_sim_download_force_field(FluidSim* sim, float* xy);
+/* the uniform the last tick used (reference: simulation_settings_bg). */
+int fluid_sim_get_uniform(const FluidSim* sim, FluidSimUniform* out);
+
+/* debug / parity taps (not in the reference API; transients of its shaders). */
+/* keys in particle order as written by create_spatial_lookup, before the sort. */
+int fluid_sim_download_unsorted_keys(FluidSim* sim, uint32_t* dst);
+/* pressure+viscosity acceleration per particle (compute.wgsl:90-93) and the sum of
+ * |terms| that the cancellation-aware tolerance uses. Enable before the tick. */
+int fluid_sim_enable_debug_force(FluidSim* sim, int enable);
+int fluid_sim_download_debug_force(FluidSim* sim, float* accel_xy, float* abs_terms_xy);
+/* sorted-order permutation of the last tick: sorted index -> index before the sort. */
+int fluid_sim_download_permutation(FluidSim* sim, uint32_t* dst);
+
+/* zero-copy accessors for device-side consumers (renderer kernels, NCCL halo exchange).
+ * Pointers stay valid until destroy; contents are ordered on fluid_sim_stream(). */
+typedef struct FluidSimDeviceView {
+    uint32_t particle_count;
+    uint32_t capacity;
+    void* position;           /* float2[N]  current positions, sorted order */
+    void* predicted_position; /* float2[N] */
+    void* velocity;           /* float2[N] */
+    void* density;            /* float[N] */
+    void* grid;               /* uint32[N] sorted keys */
+    void* start_indices;      /* uint32[grid_w*grid_h] reference-compatible table */
+    void* cell_lower_bound;   /* uint32[grid_w*grid_h+1] dense clean table */
+    void* force_field;        /* float2[tex_w*tex_h] */
+} FluidSimDeviceView;
+int fluid_sim_device_view(FluidSim* sim, FluidSimDeviceView* out);
+void* fluid_sim_stream(FluidSim* sim); /* cudaStream_t */
+
+/* per-kernel device timing of the most recent tick recorded with timing enabled
+ * (CUDA events on the handle's stream). names/ms arrays hold up to `cap` entries;
+ * returns the number of phases written. */
+int fluid_sim_enable_timing(FluidSim* sim, int enable);
+int fluid_sim_last_timing(FluidSim* sim, const char** names, float* ms, int cap);
+/* number of kernels this library has launched on the handle since creation. */
+uint64_t fluid_sim_launch_count(const FluidSim* sim);
+
+/* ---- slab (multi-GPU) support: the handle may own a y-slab of the domain ------- */
+
+/* Replace the particle set (count may change, <= capacity given at creation via
+ * fluid_sim_reserve). Used by migration / halo refresh. */
+int fluid_sim_reserve(FluidSim* sim, uint32_t capacity);
+int fluid_sim_set_particle_count(FluidSim* sim, uint32_t n);
+
+/* ---- jump-flood distance field (reference: shaders/jump_flood.wgsl:17-65; the host
+ *      protocol is pinned in SURVEY.md §8 row a7) ---------------------------------- */
+
+#define FLUID_JFA_INVALID 32767u
+
+/* Full JFA: seeds_in/out are rg32uint images (w*h pairs of u32), host pointers.
+ * jumps 2^(ceil(log2 max(w,h))-1) .. 1, strict ping-pong. */
+int fluid_jfa_run(const uint32_t* seeds_in, uint32_t w, uint32_t h, uint32_t* seeds_out, int device_ordinal);
+/* one pass with an explicit jump (reference entry point `floodfill`). */
+int fluid_jfa_pass(const uint32_t* seeds_in, uint32_t w, uint32_t h, uint32_t jump, uint32_t* seeds_out, int device_ordinal);
+/* seed image from a u8 mask with the seed rule of src/main.rs:413-438 (> 128, border fallback). */
+int fluid_jfa_seed_from_mask(const uint8_t* mask, uint32_t w, uint32_t h, uint32_t* seeds_out, int device_ordinal);
+/* seed image from predicted positions with the texel mapping of compute.wgsl:127-128. */
+int fluid_jfa_seed_from_particles(const FluidParticle* particles, uint32_t n, const float bounds[2],
+                                  uint32_t w, uint32_t h, uint32_t* seeds_out, int device_ordinal);
+/* field = -(pixel - seed) as float pairs (sign / zero rule of src/main.rs:493-511). */
+int fluid_jfa_to_force_field(const uint32_t* seeds, uint32_t w, uint32_t h, float* field_xy, int device_ordinal);
+
+/* Device-resident pipeline: particles of `sim` -> seeds -> JFA -> field, written into
+ * caller-provided host buffers if non-null; when into_sim != 0 and (w,h) equals the
+ * sim's texture size the field is also installed as the sim's force field.
+ * ms_out (optional) receives the device time of the JFA passes only. */
+int fluid_sim_jfa_from_particles(FluidSim* sim, uint32_t w, uint32_t h, uint32_t* seeds_out,
+                                 float* field_xy_out, int into_sim, float* ms_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLUID_B200_H */

@@ -1,0 +1,2 @@
+"""CPU oracle (TEST INFRASTRUCTURE ONLY). See fluid_oracle.cpp. Importable only from tests/, bench.py's
+cpu_baseline / --impl reference legs and __graft_entry__.smoke()."""
