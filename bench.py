@@ -1,0 +1,277 @@
+#!/usr/bin/env python
+"""bench.py — particle-steps/s of the full SPH fluid step (BASELINE.json metric) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload 64m-u|16m-u|4m-u|1m-u|1m-d] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+A "step" is one complete tick (predict, hash, sort, cell tables, density, force+integrate) of the workload.
+Default workload: the 64M-particle uniform box of BASELINE.json config 5 (the size the metric's target is quoted
+on; ~4 GB of particle state, far larger than the 126 MB L2, so no L2 flush is needed between steps). At N > 1 the
+same 64M box is partitioned into y-slabs over the ranks (strong scaling), with NCCL halo exchange and migration.
+
+One JSON line is printed by rank 0. `value` is device-timed (CUDA events on the library's stream, inputs resident
+in HBM); `e2e` is measured through the public API with HOST buffers (pinned upload of the full particle state +
+tick + download of the full state every step). `roofline` is for the dominant kernel (force+integrate) with its
+duration measured live by the library's per-phase CUDA events inside the timed region. `cpu_baseline` times the
+CPU oracle (the restatement of the reference's WGSL; the reference itself cannot run here) on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {  # name -> (kind, args)
+    "64m-u": ("uniform", 8000), "16m-u": ("uniform", 4000), "4m-u": ("uniform", 2000), "1m-u": ("uniform", 1000),
+    "1m-d": ("dam", (500, 2000)), "4m-d": ("dam", (1000, 4000)), "default": ("default", None),
+}
+# algorithmic bytes per particle-step, by pass
+ALGO_BYTES = {"predict+key+hist": 28, "sort": 52, "gather+cells": 52 + 8, "density": 16, "force+integrate": 44}
+ALGO_BYTES_TOTAL = 200
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """samples nvidia-smi SM clocks + throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in self.lines:
+            parts = [x.strip() for x in l.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, parts[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_scene(name):
+    from gpu_fluid_simulation_b200 import SimulationSettings, TickSettings, scenes
+    kind, arg = WORKLOADS[name]
+    if kind == "uniform":
+        return scenes.uniform_box(arg)
+    if kind == "dam":
+        return scenes.dam_break(*arg)
+    return SimulationSettings(), TickSettings(), None  # default lattice is built by create()
+
+
+def cpu_sample_scene(workload):
+    """bounded sample of the workload for the CPU arm: same spacing / h / parameters, 1M (or 256K) particles."""
+    from gpu_fluid_simulation_b200 import scenes
+    kind, _ = WORKLOADS[workload]
+    if kind == "dam":
+        return scenes.dam_break(500, 2000), "1M-particle dam-break (same spacing, h and tick parameters)"
+    return scenes.uniform_box(1000), "1M-particle sub-box of the uniform box (same spacing, h, jitter and tick parameters)"
+
+
+def run_cpu(workload, ticks, warmup=1, budget_s=25.0):
+    """times the CPU oracle (port of the reference's WGSL step; counting sort = the fair CPU variant)."""
+    from oracle import oracle as O
+    O.build()
+    (s, ts, p), desc = cpu_sample_scene(workload)
+    sim = O.OracleSim(s, p, sort_mode=O.SORT_COUNTING)
+    for _ in range(warmup):
+        sim.tick(ts)
+    t0 = time.perf_counter()
+    done = 0
+    per = []
+    while done < ticks:
+        t1 = time.perf_counter()
+        sim.tick(ts)
+        per.append(time.perf_counter() - t1)
+        done += 1
+        if budget_s and time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    n = s.particle_count
+    return {"value": n * done / dt, "unit": "particle-steps/s", "cores": int(O.lib().oracle_num_threads()), "kind": "port",
+            "sample": f"{done} ticks of a {desc}; OpenMP over particles, stable counting sort", "ms_per_step": 1e3 * dt / done,
+            "particles": n, "ticks": done}
+
+
+def reference_arm(args, rank):
+    if rank != 0:
+        return
+    t_budget = 150.0
+    r = run_cpu(args.workload, args.steps, warmup=max(1, min(args.warmup, 2)), budget_s=t_budget)
+    line = {"impl": "reference", "metric": "particle-steps/sec", "value": r["value"], "unit": "particle-steps/s",
+            "n_gpus": args.gpus, "steps": r["ticks"], "warmup": max(1, min(args.warmup, 2)), "ms_per_step": r["ms_per_step"],
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "note": "CPU oracle (C++ restatement of the reference's WGSL step; the "
+                       "reference's own wgpu/WGSL path is unavailable on this box) on a bounded sample of the workload"},
+            "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": r["value"], "unit": "particle-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="64m-u", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank)
+        return
+    if world != args.gpus:
+        if args.gpus == 1 and world == 1:
+            pass
+        else:
+            raise SystemExit(f"--gpus {args.gpus} needs WORLD_SIZE={args.gpus} (launch with torch.distributed.run); got {world}")
+
+    import torch
+    import gpu_fluid_simulation_b200 as fluid
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the fluid step has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        from gpu_fluid_simulation_b200.slab import run_slab_bench
+        line = run_slab_bench(args, rank, world, local_rank)
+        if rank == 0:
+            print(json.dumps(line), flush=True)
+        return
+
+    peak, peak_src = peaks()
+    s, ts, p = make_scene(args.workload)
+    n = s.particle_count
+    sim = fluid.FluidSimulation.new(local_rank, s)
+    if p is not None:
+        sim.upload_particles(p)
+    sim.sync()
+    stream = torch.cuda.ExternalStream(sim.stream, device=local_rank)
+
+    # ---- device-resident throughput -------------------------------------------------------------
+    sim.tick_n(ts, args.warmup)
+    sim.sync()
+    launches0 = sim.launch_count
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    sim.enable_timing(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        sim.tick_n(ts, args.steps)
+        e1.record(stream)
+    sim.sync()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop()
+    phases = sim.last_timing()
+    sim.enable_timing(False)
+    launches = sim.launch_count - launches0
+    ms_per_step = ms / args.steps
+    value = n * args.steps / (ms * 1e-3)
+
+    ph = dict(phases)
+    dom = max(ph, key=ph.get)
+    dom_ms = ph[dom]
+    achieved = ALGO_BYTES[dom] * n / (dom_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": {"force+integrate": "k_force_integrate", "density": "k_density", "sort": "k_onesweep_pass",
+                                            "predict+key+hist": "k_predict_key_hist", "gather+cells": "k_gather_cells"}[dom],
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "algorithmic_bytes_per_particle": ALGO_BYTES[dom], "kernel_ms": dom_ms,
+                "share_of_step": dom_ms / ms_per_step,
+                "whole_step": {"algorithmic_bytes_per_particle": ALGO_BYTES_TOTAL,
+                               "achieved": ALGO_BYTES_TOTAL * n / (ms_per_step * 1e-3) / 1e9,
+                               "frac": ALGO_BYTES_TOTAL * n / (ms_per_step * 1e-3) / 1e9 / peak},
+                "phases_ms": {k: round(v, 5) for k, v in phases},
+                "phase_frac_of_peak": {k: round(ALGO_BYTES[k] * n / (v * 1e-3) / 1e9 / peak, 4) for k, v in phases if v > 0}}
+    traffic_path = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_path):
+        with open(traffic_path) as f:
+            tj = json.load(f)
+        roofline["traffic"] = tj.get(args.workload, {}).get(roofline["kernel"])
+
+    # ---- end to end through the public API with host buffers -------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        host_in = torch.empty((n, 8), dtype=torch.float32).pin_memory()
+        host_out = torch.empty((n, 8), dtype=torch.float32).pin_memory()
+        init = sim.download_particles()
+        host_in.numpy().view(np.uint8).reshape(-1)[:] = init.view(np.uint8).reshape(-1)
+        del init
+        k = max(1, args.e2e_steps)
+        for _ in range(1):
+            sim.upload_particles(host_in); sim.tick(ts); sim.download_particles(out=host_out.numpy().view(fluid.PARTICLE_DTYPE).reshape(-1))
+        t0 = time.perf_counter()
+        for _ in range(k):
+            sim.upload_particles(host_in)
+            sim.tick(ts)
+            sim.download_particles(out=host_out.numpy().view(fluid.PARTICLE_DTYPE).reshape(-1))  # synchronises
+        dt = time.perf_counter() - t0
+        e2e = {"value": n * k / dt, "unit": "particle-steps/s", "h2d_bytes_per_step": n * 32 + 60, "d2h_bytes_per_step": n * 32,
+               "steps": k, "ms_per_step": 1e3 * dt / k,
+               "note": "upload_particles (pinned host AoS) + tick + download_particles (pinned host AoS) every step"}
+        del host_in, host_out
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        sim.close()
+        cpu = run_cpu(args.workload, 8, warmup=1, budget_s=20.0)
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+
+    line = {"metric": "particle-steps/sec", "value": value, "unit": "particle-steps/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "particles": n,
+                       "l2": "inputs larger than L2 (no flush)" if n * 64 > 126e6 * 2 else "state fits L2; steps run back to back as in the real simulation loop (no flush)",
+                       "parallelism": "1 GPU"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

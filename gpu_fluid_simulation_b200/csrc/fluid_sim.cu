@@ -174,8 +174,9 @@ DevParams Sim::make_params(const FluidSimUniform& u) const {
 void Sim::mark(const char* name) {
     if (!timing) return;
     if (n_marks >= MAX_MARKS) return;
-    if (!mark_events[n_marks]) cudaEventCreate(&mark_events[n_marks]);
-    cudaEventRecord(mark_events[n_marks], stream);
+    cudaEvent_t& ev = mark_events[timed_ticks % TIMING_RING][n_marks];
+    if (!ev) cudaEventCreate(&ev);
+    cudaEventRecord(ev, stream);
     mark_names[n_marks] = name;
     n_marks++;
 }
@@ -246,6 +247,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
         FLUID_CUDA(cudaMemcpyAsync(pos_a, pos_s, (size_t)n * 8, cudaMemcpyDeviceToDevice, stream));
         FLUID_CUDA(cudaMemcpyAsync(vel_a, vel_s, (size_t)n * 8, cudaMemcpyDeviceToDevice, stream));
         mark("copy");
+        if (timing) { marks_per_tick = n_marks; timed_ticks++; }
         FLUID_CUDA(cudaGetLastError());
         return FLUID_OK;
     }
@@ -261,6 +263,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
                                                                     force_field, d_frame_time, pos_a, vel_a, nullptr, nullptr);
     launches++;
     mark("force+integrate");
+    if (timing) { marks_per_tick = n_marks; timed_ticks++; }
     FLUID_CUDA(cudaGetLastError());
     return FLUID_OK;
 }
@@ -366,7 +369,7 @@ void fluid_sim_destroy(FluidSim* h) {
                     s->idx_b, s->sort_scratch, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
                     s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b};
     for (void* b : bufs) if (b) cudaFree(b);
-    for (auto& e : s->mark_events) if (e) cudaEventDestroy(e);
+    for (auto& row : s->mark_events) for (auto& e : row) if (e) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);
     cudaGetLastError();
     delete s;
@@ -525,17 +528,26 @@ int fluid_sim_enable_timing(FluidSim* h, int enable) {
     SIM_OR_FAIL(h);
     s->timing = enable != 0;
     s->n_marks = 0;
+    s->marks_per_tick = 0;
+    s->timed_ticks = 0;
     return FLUID_OK;
 }
 int fluid_sim_last_timing(FluidSim* h, const char** names, float* ms, int cap) {
     SIM_OR_FAIL(h);
     FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    if (s->timed_ticks == 0) return 0;
+    const uint64_t ticks = s->timed_ticks < (uint64_t)TIMING_RING ? s->timed_ticks : (uint64_t)TIMING_RING;
     int out = 0;
-    for (int k = 1; k < s->n_marks && out < cap; k++, out++) {
-        float t = 0.f;
-        FLUID_CUDA(cudaEventElapsedTime(&t, s->mark_events[k - 1], s->mark_events[k]));
+    for (int k = 1; k < s->marks_per_tick && out < cap; k++, out++) {
+        double sum = 0.0;
+        for (uint64_t t = 0; t < ticks; t++) {
+            const uint64_t slot = (s->timed_ticks - 1 - t) % TIMING_RING;
+            float dt = 0.f;
+            FLUID_CUDA(cudaEventElapsedTime(&dt, s->mark_events[slot][k - 1], s->mark_events[slot][k]));
+            sum += dt;
+        }
         if (names) names[out] = s->mark_names[k];
-        if (ms) ms[out] = t;
+        if (ms) ms[out] = (float)(sum / (double)ticks);
     }
     return out;
 }

@@ -12,7 +12,7 @@
 // exactly the reference's visiting order (rows y-1, y, y+1; cells x-1, x, x+1; ascending index in a
 // cell), so every fp32 sum is accumulated in the reference's order.
 //   * density walks 3x3 cells, not the reference's 7x7: the outer rings only ever add +0.0
-//     (cell size == h); tests compare against the 7x7 oracle.
+//     (cell size == h); tests compare against the 7x7 CPU restatement.
 //   * pressure and viscosity are accumulated in ONE walk with separate accumulators: same order, same
 //     bits as the reference's two walks, half the traffic.
 //   * move_particle reads neighbour velocity from the sorted snapshot and writes the new state to a
@@ -142,7 +142,7 @@ __device__ __forceinline__ float density_walk(const DevParams& p, const float2* 
             const float2 q = s[j];
             const float dx = fsub(q.x, px), dy = fsub(q.y, py);
             const float r2 = fadd(fmul(dx, dx), fmul(dy, dy));
-            if (r2 <= p.h2) {  // funcs.wgsl:74 (r2 > h2 -> 0, and +0 does not change the sum)
+            if (!(r2 > p.h2)) {  // funcs.wgsl:74: r2 > h2 -> 0 (+0 leaves the sum unchanged); NaN falls through, as there
                 const float diff = fsub(p.h2, r2);
                 const float k = fmul(fmul(fmul(p.poly6_norm, diff), diff), diff);
                 density = fadd(density, fmul(p.mass, k));

@@ -6,7 +6,8 @@ namespace fluid {
 
 constexpr int SORT_ITEMS = 16;                          // keys per thread per onesweep tile
 constexpr uint32_t SORT_TILE = SORT_THREADS * SORT_ITEMS;
-constexpr int MAX_MARKS = 16;
+constexpr int MAX_MARKS = 12;
+constexpr int TIMING_RING = 256;
 
 struct Sim {
     int device = 0;
@@ -44,9 +45,12 @@ struct Sim {
     uint32_t *jfa_a = nullptr, *jfa_b = nullptr;  // packed seed ping-pong for fluid_sim_jfa_from_particles
     size_t jfa_pixels = 0;
 
+    // per-phase device timing: a ring of TIMING_RING ticks x MAX_MARKS events on `stream`
     bool timing = false;
-    int n_marks = 0;
-    cudaEvent_t mark_events[MAX_MARKS] = {};
+    int n_marks = 0;                 // marks recorded in the tick being enqueued
+    int marks_per_tick = 0;          // marks of the last completed enqueue
+    uint64_t timed_ticks = 0;        // ticks enqueued since timing was enabled
+    cudaEvent_t mark_events[TIMING_RING][MAX_MARKS] = {};
     const char* mark_names[MAX_MARKS] = {};
     uint64_t launches = 0;
 

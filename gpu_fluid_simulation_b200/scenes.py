@@ -1,6 +1,6 @@
 """Synthetic scenes of SURVEY.md §8(d): uniform box (U) and dam-break (D).
 
-Inputs are generated once on the host (splitmix64, fixed seeds) and handed identically to the oracle
+Inputs are generated once on the host (splitmix64, fixed seeds) and handed identically to the CPU checker
 and to the CUDA library through upload_particles, so the PRNG is not part of parity.
 """
 import numpy as np

@@ -185,9 +185,9 @@ typedef struct FluidSimDeviceView {
 int fluid_sim_device_view(FluidSim* sim, FluidSimDeviceView* out);
 void* fluid_sim_stream(FluidSim* sim); /* cudaStream_t */
 
-/* per-kernel device timing of the most recent tick recorded with timing enabled
- * (CUDA events on the handle's stream). names/ms arrays hold up to `cap` entries;
- * returns the number of phases written. */
+/* per-phase device timing (CUDA events on the handle's stream), averaged over the ticks
+ * enqueued since timing was enabled (the most recent 256 at most). names/ms arrays hold up to
+ * `cap` entries; returns the number of phases written. Synchronises the stream. */
 int fluid_sim_enable_timing(FluidSim* sim, int enable);
 int fluid_sim_last_timing(FluidSim* sim, const char** names, float* ms, int cap);
 /* number of kernels this library has launched on the handle since creation. */
