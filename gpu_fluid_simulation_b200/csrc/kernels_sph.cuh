@@ -28,89 +28,105 @@ namespace fluid {
 constexpr int SPH_THREADS = 256;
 constexpr int SPH_CAP = 1536;  // staged particles per CTA (3 row spans of ~256+2 cells, rounded)
 
+constexpr int SPH_MAX_ROWS = 2;  // CTA row groups that get their own three staged spans
+
 struct SpanPlan {
-    // per grid row r (0..2 = y-1, y, y+1 in the single-row case): global index of the first staged
-    // particle minus its offset in the staging buffer, so smem index = global index - base[r]
-    int base[3];
+    // base[g*3 + r]: for a thread whose cell row is row_first + g, and neighbour row r (0..2 = y-1, y, y+1):
+    // global index of the first staged particle of that span minus its offset in the staging buffer,
+    // so staging index = global index - base. In the single-interval case all entries are equal.
+    int base[SPH_MAX_ROWS * 3];
+    uint32_t row_first;
     int staged;  // 1: spans are in shared memory; 0: walk global memory
 };
 
 // thread-0 planning: which global index intervals does this CTA need, do they fit, issue the copies.
 // arrays[k] / smem[k] / elem_bytes[k]: the SoA streams to stage (1 for density, 3 for force).
+//   * CTA within <= SPH_MAX_ROWS grid rows: per row group g, the cells [x_lo-1, x_hi+1] of rows y-1, y, y+1,
+//     where [x_lo, x_hi] bounds the CTA's particles of that row (3 spans per group);
+//   * more rows (short rows): one span from (first row - 1, x_first - 1) to (last row + 1, x_last + 1);
+//   * if the spans exceed SPH_CAP particles the CTA walks global memory instead.
 template <int NARR>
 __device__ __forceinline__ void plan_and_stage(const DevParams& p, uint32_t i0, uint32_t i1,
                                                const uint32_t* __restrict__ keys, const uint32_t* __restrict__ lb,
                                                const void* const (&arrays)[NARR], void* const (&smem)[NARR],
                                                const uint32_t (&elem_bytes)[NARR], uint64_t* bar, SpanPlan* plan) {
+    constexpr int NI = SPH_MAX_ROWS * 3;
     const uint32_t kf = min(__ldg(keys + i0), p.num_cells - 1u), kl = min(__ldg(keys + i1 - 1u), p.num_cells - 1u);
     const uint32_t yf = kf / p.grid_w, xa = kf - yf * p.grid_w;
     const uint32_t yl = kl / p.grid_w, xb = kl - yl * p.grid_w;
-    uint32_t lo[3], hi[3];
-    int nint;
-    if (yf == yl) {
-        nint = 3;
+    const uint32_t nrows = yl - yf + 1u;
+    uint32_t lo[NI], hi[NI];
 #pragma unroll
-        for (int r = 0; r < 3; r++) {
-            const uint32_t row = yf + (uint32_t)r - 1u;  // wraps for yf == 0 -> fails the range test
-            if (row < p.grid_h) {
-                const uint32_t ca = row * p.grid_w + (xa > 0u ? xa - 1u : 0u);
-                const uint32_t cb = row * p.grid_w + min(xb + 2u, p.grid_w);
-                lo[r] = __ldg(lb + ca);
-                hi[r] = __ldg(lb + cb);
-            } else {
-                lo[r] = 0; hi[r] = 0;
+    for (int t = 0; t < NI; t++) { lo[t] = 0; hi[t] = 0; }
+    plan->row_first = yf;
+    const bool grouped = nrows <= (uint32_t)SPH_MAX_ROWS;
+    if (grouped) {
+#pragma unroll
+        for (int g = 0; g < SPH_MAX_ROWS; g++) {
+            if ((uint32_t)g < nrows) {
+                const uint32_t y = yf + (uint32_t)g;
+                const uint32_t x_lo = (g == 0) ? xa : 0u;
+                const uint32_t x_hi = ((uint32_t)g == nrows - 1u) ? xb : p.grid_w - 1u;
+#pragma unroll
+                for (int r = 0; r < 3; r++) {
+                    const uint32_t row = y + (uint32_t)r - 1u;  // wraps for y == 0 -> fails the range test
+                    if (row < p.grid_h) {
+                        lo[g * 3 + r] = __ldg(lb + row * p.grid_w + (x_lo > 0u ? x_lo - 1u : 0u));
+                        hi[g * 3 + r] = __ldg(lb + row * p.grid_w + min(x_hi + 2u, p.grid_w));
+                    }
+                }
             }
         }
     } else {
-        nint = 1;
         const uint32_t ca = yf > 0u ? (yf - 1u) * p.grid_w + (xa > 0u ? xa - 1u : 0u) : 0u;
         const uint32_t cb = (yl + 1u < p.grid_h) ? (yl + 1u) * p.grid_w + min(xb + 2u, p.grid_w) : p.num_cells;
         lo[0] = __ldg(lb + ca);
         hi[0] = __ldg(lb + cb);
-        lo[1] = lo[2] = hi[1] = hi[2] = 0;
     }
     // 16-byte granularity for every stream: round to multiples of 4 particles
-    uint32_t total = 0, off[3];
+    uint32_t total = 0, off[NI];
 #pragma unroll
-    for (int r = 0; r < 3; r++) {
-        lo[r] &= ~3u;
-        hi[r] = (hi[r] + 3u) & ~3u;
-        if (hi[r] < lo[r]) hi[r] = lo[r];
-        off[r] = total;
-        total += hi[r] - lo[r];
+    for (int t = 0; t < NI; t++) {
+        lo[t] &= ~3u;
+        hi[t] = (hi[t] + 3u) & ~3u;
+        if (hi[t] < lo[t]) hi[t] = lo[t];
+        off[t] = total;
+        total += hi[t] - lo[t];
     }
     if (total > (uint32_t)SPH_CAP) {
         plan->staged = 0;
-        plan->base[0] = plan->base[1] = plan->base[2] = 0;
         return;
     }
     plan->staged = 1;
-    if (nint == 3) {
 #pragma unroll
-        for (int r = 0; r < 3; r++) plan->base[r] = (int)lo[r] - (int)off[r];
-    } else {
-        plan->base[0] = plan->base[1] = plan->base[2] = (int)lo[0];
-    }
+    for (int t = 0; t < NI; t++) plan->base[t] = grouped ? (int)lo[t] - (int)off[t] : (int)lo[0];
     uint32_t bytes = 0;
 #pragma unroll
     for (int k = 0; k < NARR; k++) bytes += total * elem_bytes[k];
-    if (bytes == 0) { mbar_arrive_expect_tx(bar, 0); return; }
     mbar_arrive_expect_tx(bar, bytes);
 #pragma unroll
-    for (int r = 0; r < 3; r++) {
-        const uint32_t len = hi[r] - lo[r];
+    for (int t = 0; t < NI; t++) {
+        const uint32_t len = hi[t] - lo[t];
         if (len == 0) continue;
 #pragma unroll
         for (int k = 0; k < NARR; k++) {
-            bulk_g2s(reinterpret_cast<char*>(smem[k]) + (size_t)off[r] * elem_bytes[k],
-                     reinterpret_cast<const char*>(arrays[k]) + (size_t)lo[r] * elem_bytes[k], len * elem_bytes[k], bar);
+            bulk_g2s(reinterpret_cast<char*>(smem[k]) + (size_t)off[t] * elem_bytes[k],
+                     reinterpret_cast<const char*>(arrays[k]) + (size_t)lo[t] * elem_bytes[k], len * elem_bytes[k], bar);
         }
     }
 }
 
+// staging-buffer bases for a thread in cell row `cy`
+__device__ __forceinline__ void thread_bases(const SpanPlan& plan, uint32_t cy, int (&base)[3]) {
+    uint32_t g = cy - plan.row_first;
+    if (g >= (uint32_t)SPH_MAX_ROWS) g = 0;  // single-interval plans: all entries equal
+#pragma unroll
+    for (int r = 0; r < 3; r++) base[r] = plan.base[g * 3 + r];
+}
+
 // this thread's three spans [a[r], b[r]) in global sorted-index space
-__device__ __forceinline__ void thread_spans(const DevParams& p, uint32_t key, const uint32_t* __restrict__ lb,
-                                             uint32_t c0, uint32_t s_stale, uint32_t (&a)[3], uint32_t (&b)[3]) {
+__device__ __forceinline__ uint32_t thread_spans(const DevParams& p, uint32_t key, const uint32_t* __restrict__ lb,
+                                                 uint32_t c0, uint32_t s_stale, uint32_t (&a)[3], uint32_t (&b)[3]) {
     const uint32_t k = min(key, p.num_cells - 1u);
     const uint32_t cy = k / p.grid_w, cx = k - cy * p.grid_w;
 #pragma unroll
@@ -122,10 +138,13 @@ __device__ __forceinline__ void thread_spans(const DevParams& p, uint32_t key, c
             const uint32_t cb = row * p.grid_w + min(cx + 2u, p.grid_w);  // column grid_w is the next row's empty column 0
             uint32_t lo = __ldg(lb + ca), hi = __ldg(lb + cb);
             // lowest occupied cell: the reference walks it from its stale start_indices entry
-            if (ca <= c0 && c0 < cb) lo = min(max(lo, s_stale), hi);
+            // (only that cell: if the stale entry is past its end the cell reads as empty, the cells after it
+            // in the span are unaffected)
+            if (ca <= c0 && c0 < cb) lo = min(max(lo, s_stale), __ldg(lb + c0 + 1u));
             a[r] = lo; b[r] = hi;
         }
     }
+    return cy;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -172,8 +191,9 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
     const bool valid = i < p.n;
     uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
     float2 me = make_float2(0.f, 0.f);
+    uint32_t cy = 0;
     if (valid) {
-        thread_spans(p, __ldg(keys + i), lb, __ldg(quirk), __ldg(quirk + 1), a, b);
+        cy = thread_spans(p, __ldg(keys + i), lb, __ldg(quirk), __ldg(quirk + 1), a, b);
         me = __ldg(pred_s + i);
     }
     __syncthreads();
@@ -181,7 +201,8 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
     float d;
     if (staged) {
         mbar_wait(&s_bar, 0);
-        const int base[3] = {s_plan.base[0], s_plan.base[1], s_plan.base[2]};
+        int base[3];
+        thread_bases(s_plan, valid ? cy : s_plan.row_first, base);
         d = density_walk<true>(p, s_pred, base, a, b, me.x, me.y);
     } else {
         const int base[3] = {0, 0, 0};
@@ -219,52 +240,111 @@ struct ForceAcc {
     float ax, ay;  // sum of |terms| (debug only)
 };
 
-template <bool STAGED, bool DEBUG>
-__device__ __forceinline__ void force_walk(const DevParams& p, const float2* __restrict__ pred, const float2* __restrict__ vel,
-                                           const float* __restrict__ rho, const int (&base)[3], const uint32_t (&a)[3],
-                                           const uint32_t (&b)[3], uint32_t self, float px, float py, float vx, float vy,
-                                           float pressure, uint32_t& rand_seed, ForceAcc& acc) {
+// one accepted neighbour: pressure term (compute.wgsl:206-223) and viscosity term (:283-288), each added
+// to its own accumulator in visiting order
+template <bool DEBUG>
+__device__ __forceinline__ void force_pair(const DevParams& p, float dx, float dy, float sq, float2 nv, float nd, float vx,
+                                           float vy, float pressure, uint32_t& rand_seed, ForceAcc& acc) {
+    const float dst = fsqrt(sq);
+    float dirx, diry;
+    if (dst == 0.0f) {  // compute.wgsl:211-212
+        const float rx = rand_f32(rand_seed);
+        const float ry = rand_f32(rand_seed);
+        const float len = fsqrt(fadd(fmul(rx, rx), fmul(ry, ry)));
+        dirx = fdiv(rx, len); diry = fdiv(ry, len);
+    } else {
+        dirx = fdiv(dx, dst); diry = fdiv(dy, dst);
+    }
+    const float np = fmul(p.pressure_constant, fsub(nd, p.rest_density));
+    const float k = (dst <= p.h) ? fmul(-fsub(p.h, dst), p.spiky) : 0.0f;  // funcs.wgsl:101-109
+    const float shared_p = fmul(fadd(pressure, np), 0.5f);
+    const float tx = fdiv(fmul(fmul(dirx, k), shared_p), nd);
+    const float ty = fdiv(fmul(fmul(diry, k), shared_p), nd);
+    acc.px = fadd(acc.px, tx);
+    acc.py = fadd(acc.py, ty);
+    const float kv = viscosity_kernel(p, dst);
+    const float ux = fmul(fdiv(fsub(nv.x, vx), nd), kv);  // compute.wgsl:288
+    const float uy = fmul(fdiv(fsub(nv.y, vy), nd), kv);
+    acc.vx = fadd(acc.vx, ux);
+    acc.vy = fadd(acc.vy, uy);
+    if (DEBUG) {
+        acc.ax += fabsf(tx) + fabsf(ux) * p.visc_coef;
+        acc.ay += fabsf(ty) + fabsf(uy) * p.visc_coef;
+    }
+}
+
+// fallback walk straight from global memory (CTAs whose neighbourhood does not fit the staging buffer)
+template <bool DEBUG>
+__device__ __forceinline__ void force_walk_global(const DevParams& p, const float2* __restrict__ pred,
+                                                  const float2* __restrict__ vel, const float* __restrict__ rho,
+                                                  const uint32_t (&a)[3], const uint32_t (&b)[3], uint32_t self, float px,
+                                                  float py, float vx, float vy, float pressure, uint32_t& rand_seed,
+                                                  ForceAcc& acc) {
 #pragma unroll
     for (int r = 0; r < 3; r++) {
-        const int bs = STAGED ? base[r] : 0;
-        const float2* sp = pred - bs;
-        const float2* sv = vel - bs;
-        const float* sr = rho - bs;
         for (uint32_t j = a[r]; j < b[r]; j++) {
             if (j == self) continue;  // compute.wgsl:195
-            const float2 q = sp[j];
+            const float2 q = pred[j];
             const float dx = fsub(q.x, px), dy = fsub(q.y, py);
             const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
             if (sq > p.h2) continue;  // compute.wgsl:202 (sqr_radius == h*h)
-            const float dst = fsqrt(sq);
-            const float nd = sr[j];
-            const float2 nv = sv[j];
-            float dirx, diry;
-            if (dst == 0.0f) {  // compute.wgsl:211-212
-                const float rx = rand_f32(rand_seed);
-                const float ry = rand_f32(rand_seed);
-                const float len = fsqrt(fadd(fmul(rx, rx), fmul(ry, ry)));
-                dirx = fdiv(rx, len); diry = fdiv(ry, len);
-            } else {
-                dirx = fdiv(dx, dst); diry = fdiv(dy, dst);
+            force_pair<DEBUG>(p, dx, dy, sq, vel[j], rho[j], vx, vy, pressure, rand_seed, acc);
+        }
+    }
+}
+
+// Staged walk, in two alternating warp-synchronous phases so that the expensive pair evaluation runs with
+// (nearly) all lanes active: only ~1/3 of the candidates in the 3x3 cells are within h, and evaluating
+// inside the candidate loop would execute the ~130-instruction pair body for a warp whenever ANY lane
+// accepts. Phase A scans candidates (cheap distance test) and appends accepted staging-buffer indices to
+// a per-thread list of up to FORCE_LIST entries, in visiting order; phase B evaluates the list in that
+// order. Visiting order, hence every fp32 sum, is unchanged.
+constexpr int FORCE_LIST = 16;
+
+template <bool DEBUG>
+__device__ __forceinline__ void force_walk_staged(const DevParams& p, const float2* __restrict__ sp,
+                                                  const float2* __restrict__ sv, const float* __restrict__ sr,
+                                                  uint16_t* __restrict__ list /* [FORCE_LIST][SPH_THREADS], this thread's column */,
+                                                  const int (&base)[3], const uint32_t (&a)[3], const uint32_t (&b)[3],
+                                                  uint32_t self, float px, float py, float vx, float vy, float pressure,
+                                                  uint32_t& rand_seed, ForceAcc& acc) {
+    int r = 0;
+    uint32_t j = a[0], end = b[0];
+    int off = base[0];
+    bool more = true;
+    while (__any_sync(0xffffffffu, more)) {
+        int cnt = 0;
+        // ---- phase A: scan ----
+        while (more && cnt < FORCE_LIST) {
+            if (j >= end) {  // next row span (constant indices keep a/b/base in registers)
+                if (r == 0) { j = a[1]; end = b[1]; off = base[1]; r = 1; }
+                else if (r == 1) { j = a[2]; end = b[2]; off = base[2]; r = 2; }
+                else { more = false; break; }
+                continue;
             }
-            const float np = fmul(p.pressure_constant, fsub(nd, p.rest_density));
-            const float k = (dst <= p.h) ? fmul(-fsub(p.h, dst), p.spiky) : 0.0f;  // funcs.wgsl:101-109
-            const float shared_p = fmul(fadd(pressure, np), 0.5f);
-            const float tx = fdiv(fmul(fmul(dirx, k), shared_p), nd);
-            const float ty = fdiv(fmul(fmul(diry, k), shared_p), nd);
-            acc.px = fadd(acc.px, tx);
-            acc.py = fadd(acc.py, ty);
-            const float kv = viscosity_kernel(p, dst);
-            const float ux = fmul(fdiv(fsub(nv.x, vx), nd), kv);  // compute.wgsl:288
-            const float uy = fmul(fdiv(fsub(nv.y, vy), nd), kv);
-            acc.vx = fadd(acc.vx, ux);
-            acc.vy = fadd(acc.vy, uy);
-            if (DEBUG) {
-                acc.ax += fabsf(tx) + fabsf(ux) * p.visc_coef;
-                acc.ay += fabsf(ty) + fabsf(uy) * p.visc_coef;
+            const uint32_t sidx = j - (uint32_t)off;
+            const float2 q = sp[sidx];
+            const float dx = fsub(q.x, px), dy = fsub(q.y, py);
+            const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
+            if (j != self && !(sq > p.h2)) {  // compute.wgsl:195, :202
+                list[cnt * SPH_THREADS] = (uint16_t)sidx;
+                cnt++;
+            }
+            j++;
+        }
+        __syncwarp();
+        // ---- phase B: evaluate ----
+        const int max_cnt = __reduce_max_sync(0xffffffffu, cnt);
+        for (int k = 0; k < max_cnt; k++) {
+            if (k < cnt) {
+                const uint32_t sidx = list[k * SPH_THREADS];
+                const float2 q = sp[sidx];
+                const float dx = fsub(q.x, px), dy = fsub(q.y, py);
+                const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
+                force_pair<DEBUG>(p, dx, dy, sq, sv[sidx], sr[sidx], vx, vy, pressure, rand_seed, acc);
             }
         }
+        __syncwarp();
     }
 }
 
@@ -279,6 +359,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     __shared__ __align__(128) float2 s_pred[SPH_CAP];
     __shared__ __align__(128) float2 s_vel[SPH_CAP];
     __shared__ __align__(128) float s_rho[SPH_CAP];
+    __shared__ uint16_t s_list[FORCE_LIST * SPH_THREADS];
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
     const uint32_t i0 = blockIdx.x * SPH_THREADS;
@@ -296,8 +377,9 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
     float2 pos = make_float2(0.f, 0.f), pred = pos, vel = pos;
     float dens = 1.0f;
+    uint32_t cy = 0;
     if (valid) {
-        thread_spans(p, __ldg(keys + i), lb, __ldg(quirk), __ldg(quirk + 1), a, b);
+        cy = thread_spans(p, __ldg(keys + i), lb, __ldg(quirk), __ldg(quirk + 1), a, b);
         pos = __ldg(pos_s + i);
         pred = __ldg(pred_s + i);
         vel = __ldg(vel_s + i);
@@ -310,11 +392,12 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     __syncthreads();
     if (s_plan.staged) {
         mbar_wait(&s_bar, 0);
-        const int base[3] = {s_plan.base[0], s_plan.base[1], s_plan.base[2]};
-        force_walk<true, DEBUG>(p, s_pred, s_vel, s_rho, base, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
+        int base[3];
+        thread_bases(s_plan, valid ? cy : s_plan.row_first, base);
+        force_walk_staged<DEBUG>(p, s_pred, s_vel, s_rho, s_list + threadIdx.x, base, a, b, i, pred.x, pred.y, vel.x, vel.y,
+                                 pressure, rand_seed, acc);
     } else {
-        const int base[3] = {0, 0, 0};
-        force_walk<false, DEBUG>(p, pred_s, vel_s, rho, base, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
+        force_walk_global<DEBUG>(p, pred_s, vel_s, rho, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
     }
     if (!valid) return;
 
