@@ -153,6 +153,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="64m-u", choices=sorted(WORKLOADS))
+    ap.add_argument("--math", default="exact", choices=["exact", "fast"],
+                    help="force-pass arithmetic: exact = IEEE-rounded reference order (bit-identical to the oracle); "
+                         "fast = hardware rsqrt/rcp + FMA (<= 1e-5 parity, tests/test_gpu_parity.py)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=3)
@@ -187,6 +190,7 @@ def main():
     s, ts, p = make_scene(args.workload)
     n = s.particle_count
     sim = fluid.FluidSimulation.new(local_rank, s)
+    sim.math_mode = 1 if args.math == "fast" else 0
     if p is not None:
         sim.upload_particles(p)
     sim.sync()
@@ -266,7 +270,7 @@ def main():
     line = {"metric": "particle-steps/sec", "value": value, "unit": "particle-steps/s", "n_gpus": 1, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "particles": n,
+            "config": {"workload": args.workload, "particles": n, "math": args.math,
                        "l2": "inputs larger than L2 (no flush)" if n * 64 > 126e6 * 2 else "state fits L2; steps run back to back as in the real simulation loop (no flush)",
                        "parallelism": "1 GPU"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}

@@ -168,6 +168,9 @@ DevParams Sim::make_params(const FluidSimUniform& u) const {
     p.tex_len = p.tex_wu * p.tex_hu;
     p.p2w_x = (u.bounds[0] * 2.0f) / u.texture_size[0];
     p.p2w_y = (u.bounds[1] * 2.0f) / u.texture_size[1];
+    p.inv_two_h3 = 1.0f / p.two_h3;
+    p.inv_h2 = 1.0f / p.h2;
+    p.exact_math = exact_math ? 1 : 0;
     return p;
 }
 
@@ -255,12 +258,16 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     k_density<<<sblocks, SPH_THREADS, 0, stream>>>(p, pred_s, keys_sorted, cell_lb, quirk, rho);
     launches++;
     mark("density");
-    if (debug_force)
-        k_force_integrate<true><<<sblocks, SPH_THREADS, 0, stream>>>(p, pos_s, pred_s, vel_s, rho, keys_sorted, cell_lb, quirk,
-                                                                   force_field, d_frame_time, pos_a, vel_a, dbg_accel, dbg_abs);
-    else
-        k_force_integrate<false><<<sblocks, SPH_THREADS, 0, stream>>>(p, pos_s, pred_s, vel_s, rho, keys_sorted, cell_lb, quirk,
-                                                                    force_field, d_frame_time, pos_a, vel_a, nullptr, nullptr);
+    {
+        float2* da = debug_force ? dbg_accel : nullptr;
+        float2* db = debug_force ? dbg_abs : nullptr;
+#define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                        \
+    k_force_integrate<DBG, EX><<<sblocks, SPH_THREADS, 0, stream>>>(p, pos_s, pred_s, vel_s, rho, keys_sorted, cell_lb, quirk, \
+                                                                    force_field, d_frame_time, pos_a, vel_a, da, db)
+        if (debug_force) { if (exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
+        else { if (exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
+#undef FLUID_LAUNCH_FORCE
+    }
     launches++;
     mark("force+integrate");
     if (timing) { marks_per_tick = n_marks; timed_ticks++; }
@@ -552,6 +559,16 @@ int fluid_sim_last_timing(FluidSim* h, const char** names, float* ms, int cap) {
     return out;
 }
 uint64_t fluid_sim_launch_count(const FluidSim* h) { return h ? reinterpret_cast<const Sim*>(h)->launches : 0; }
+
+int fluid_sim_set_math_mode(FluidSim* h, int mode) {
+    SIM_OR_FAIL(h);
+    if (mode != FLUID_MATH_EXACT && mode != FLUID_MATH_FAST) return invalid("fluid_sim_set_math_mode: unknown mode");
+    s->exact_math = (mode == FLUID_MATH_EXACT);
+    return FLUID_OK;
+}
+int fluid_sim_get_math_mode(const FluidSim* h) {
+    return (h && !reinterpret_cast<const Sim*>(h)->exact_math) ? FLUID_MATH_FAST : FLUID_MATH_EXACT;
+}
 
 int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
     SIM_OR_FAIL(h);

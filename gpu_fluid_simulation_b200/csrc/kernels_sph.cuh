@@ -150,23 +150,41 @@ __device__ __forceinline__ uint32_t thread_spans(const DevParams& p, uint32_t ke
 // ------------------------------------------------------------------------------------------------
 // K5 density
 // ------------------------------------------------------------------------------------------------
-template <bool STAGED>
-__device__ __forceinline__ float density_walk(const DevParams& p, const float2* __restrict__ src, const int (&base)[3],
-                                              const uint32_t (&a)[3], const uint32_t (&b)[3], float px, float py) {
+// funcs.wgsl:186-192: one candidate's contribution, added in visiting order
+__device__ __forceinline__ void density_candidate(const DevParams& p, float2 q, float px, float py, float& density) {
+    const float dx = fsub(q.x, px), dy = fsub(q.y, py);
+    const float r2 = fadd(fmul(dx, dx), fmul(dy, dy));
+    if (!(r2 > p.h2)) {  // funcs.wgsl:74: r2 > h2 -> 0 (+0 leaves the sum unchanged); NaN falls through, as there
+        const float diff = fsub(p.h2, r2);
+        const float k = fmul(fmul(fmul(p.poly6_norm, diff), diff), diff);
+        density = fadd(density, fmul(p.mass, k));
+    }
+}
+
+// fallback: straight from global memory
+__device__ __forceinline__ float density_walk_global(const DevParams& p, const float2* __restrict__ pred,
+                                                     const uint32_t (&a)[3], const uint32_t (&b)[3], float px, float py) {
     float density = 0.0f;
 #pragma unroll
-    for (int r = 0; r < 3; r++) {
-        const float2* s = src - (STAGED ? base[r] : 0);
-        for (uint32_t j = a[r]; j < b[r]; j++) {
-            const float2 q = s[j];
-            const float dx = fsub(q.x, px), dy = fsub(q.y, py);
-            const float r2 = fadd(fmul(dx, dx), fmul(dy, dy));
-            if (!(r2 > p.h2)) {  // funcs.wgsl:74: r2 > h2 -> 0 (+0 leaves the sum unchanged); NaN falls through, as there
-                const float diff = fsub(p.h2, r2);
-                const float k = fmul(fmul(fmul(p.poly6_norm, diff), diff), diff);
-                density = fadd(density, fmul(p.mass, k));
-            }
-        }
+    for (int r = 0; r < 3; r++)
+        for (uint32_t j = a[r]; j < b[r]; j++) density_candidate(p, __ldg(pred + j), px, py, density);
+    return density;
+}
+
+// staged: one iterator over the three row spans (the warp's trip count is the max over lanes of the SUM of
+// the span lengths, not the sum of the per-span maxima), explicit 32-bit shared addresses
+__device__ __forceinline__ float density_walk_staged(const DevParams& p, uint32_t sp_addr, const int (&base)[3],
+                                                     const uint32_t (&a)[3], const uint32_t (&b)[3], float px, float py) {
+    float density = 0.0f;
+    const uint32_t A1 = sp_addr + (a[1] - (uint32_t)base[1]) * 8u, E1 = sp_addr + (b[1] - (uint32_t)base[1]) * 8u;
+    const uint32_t A2 = sp_addr + (a[2] - (uint32_t)base[2]) * 8u, E2 = sp_addr + (b[2] - (uint32_t)base[2]) * 8u;
+    uint32_t addr = sp_addr + (a[0] - (uint32_t)base[0]) * 8u, end = sp_addr + (b[0] - (uint32_t)base[0]) * 8u;
+    int r = 0;
+    while (true) {
+        for (; addr < end; addr += 8u) density_candidate(p, lds_f2(addr), px, py, density);  // tight inner loop
+        if (r == 0) { addr = A1; end = E1; r = 1; }
+        else if (r == 1) { addr = A2; end = E2; r = 2; }
+        else break;
     }
     return density;
 }
@@ -203,10 +221,9 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
         mbar_wait(&s_bar, 0);
         int base[3];
         thread_bases(s_plan, valid ? cy : s_plan.row_first, base);
-        d = density_walk<true>(p, s_pred, base, a, b, me.x, me.y);
+        d = density_walk_staged(p, smem_u32_pinned(s_pred), base, a, b, me.x, me.y);
     } else {
-        const int base[3] = {0, 0, 0};
-        d = density_walk<false>(p, pred_s, base, a, b, me.x, me.y);
+        d = density_walk_global(p, pred_s, a, b, me.x, me.y);
     }
     // funcs.wgsl:202 max(density, EPSILON); compute.wgsl:70 max(.., 0.1)
     if (valid) rho[i] = fmaxf(fmaxf(d, 1.19209290e-07f), 0.1f);
@@ -241,32 +258,67 @@ struct ForceAcc {
 };
 
 // one accepted neighbour: pressure term (compute.wgsl:206-223) and viscosity term (:283-288), each added
-// to its own accumulator in visiting order
-template <bool DEBUG>
+// to its own accumulator in visiting order.
+//   EXACT: every operation IEEE-rounded in the reference's order (bit-identical to the CPU restatement).
+//   !EXACT ("fast"): one MUFU.RSQ gives 1/r (so r = sq/r', dir = d/r', h/(2r)) and one MUFU.RCP gives 1/rho_j;
+//   FMA contraction allowed; constants' reciprocals hoisted. Agrees with EXACT to a few ulp per term
+//   (tests bound it by 1e-5 of sum|terms|); branch decisions (r2 cut-off, r == 0, r <= h) are unchanged.
+template <bool DEBUG, bool EXACT>
 __device__ __forceinline__ void force_pair(const DevParams& p, float dx, float dy, float sq, float2 nv, float nd, float vx,
                                            float vy, float pressure, uint32_t& rand_seed, ForceAcc& acc) {
-    const float dst = fsqrt(sq);
-    float dirx, diry;
-    if (dst == 0.0f) {  // compute.wgsl:211-212
-        const float rx = rand_f32(rand_seed);
-        const float ry = rand_f32(rand_seed);
-        const float len = fsqrt(fadd(fmul(rx, rx), fmul(ry, ry)));
-        dirx = fdiv(rx, len); diry = fdiv(ry, len);
+    float tx, ty, ux, uy;
+    if (EXACT) {
+        const float dst = fsqrt(sq);
+        float dirx, diry;
+        if (dst == 0.0f) {  // compute.wgsl:211-212
+            const float rx = rand_f32(rand_seed);
+            const float ry = rand_f32(rand_seed);
+            const float len = fsqrt(fadd(fmul(rx, rx), fmul(ry, ry)));
+            dirx = fdiv(rx, len); diry = fdiv(ry, len);
+        } else {
+            dirx = fdiv(dx, dst); diry = fdiv(dy, dst);
+        }
+        const float np = fmul(p.pressure_constant, fsub(nd, p.rest_density));
+        const float k = (dst <= p.h) ? fmul(-fsub(p.h, dst), p.spiky) : 0.0f;  // funcs.wgsl:101-109
+        const float shared_p = fmul(fadd(pressure, np), 0.5f);
+        tx = fdiv(fmul(fmul(dirx, k), shared_p), nd);
+        ty = fdiv(fmul(fmul(diry, k), shared_p), nd);
+        acc.px = fadd(acc.px, tx);
+        acc.py = fadd(acc.py, ty);
+        const float kv = viscosity_kernel(p, dst);
+        ux = fmul(fdiv(fsub(nv.x, vx), nd), kv);  // compute.wgsl:288
+        uy = fmul(fdiv(fsub(nv.y, vy), nd), kv);
+        acc.vx = fadd(acc.vx, ux);
+        acc.vy = fadd(acc.vy, uy);
     } else {
-        dirx = fdiv(dx, dst); diry = fdiv(dy, dst);
+        float dst, dirx, diry, half_h_over_r;
+        if (sq == 0.0f) {
+            const float rx = rand_f32(rand_seed);
+            const float ry = rand_f32(rand_seed);
+            const float il = rsqrt_approx(rx * rx + ry * ry);
+            dirx = rx * il; diry = ry * il;  // (0,0) draws give NaN here as in the reference; the guard zeroes it
+            dst = 0.0f; half_h_over_r = 0.0f;
+        } else {
+            const float ir = rsqrt_approx(sq);
+            dst = sq * ir;
+            dirx = dx * ir; diry = dy * ir;
+            half_h_over_r = 0.5f * p.h * ir;
+        }
+        const float ind = rcp_approx(nd);
+        const float np = p.pressure_constant * (nd - p.rest_density);
+        const float k = (dst <= p.h) ? -(p.h - dst) * p.spiky : 0.0f;
+        const float w = k * ((pressure + np) * 0.5f) * ind;
+        tx = dirx * w; ty = diry * w;
+        acc.px += tx; acc.py += ty;
+        float kv = 0.0f;
+        if (dst <= p.h) {
+            const float r2 = dst * dst;
+            kv = (dst == 0.0f) ? p.visc_k : p.visc_k * (((-(r2 * dst) * p.inv_two_h3) + r2 * p.inv_h2 + half_h_over_r) - 1.0f);
+        }
+        const float wv = ind * kv;
+        ux = (nv.x - vx) * wv; uy = (nv.y - vy) * wv;
+        acc.vx += ux; acc.vy += uy;
     }
-    const float np = fmul(p.pressure_constant, fsub(nd, p.rest_density));
-    const float k = (dst <= p.h) ? fmul(-fsub(p.h, dst), p.spiky) : 0.0f;  // funcs.wgsl:101-109
-    const float shared_p = fmul(fadd(pressure, np), 0.5f);
-    const float tx = fdiv(fmul(fmul(dirx, k), shared_p), nd);
-    const float ty = fdiv(fmul(fmul(diry, k), shared_p), nd);
-    acc.px = fadd(acc.px, tx);
-    acc.py = fadd(acc.py, ty);
-    const float kv = viscosity_kernel(p, dst);
-    const float ux = fmul(fdiv(fsub(nv.x, vx), nd), kv);  // compute.wgsl:288
-    const float uy = fmul(fdiv(fsub(nv.y, vy), nd), kv);
-    acc.vx = fadd(acc.vx, ux);
-    acc.vy = fadd(acc.vy, uy);
     if (DEBUG) {
         acc.ax += fabsf(tx) + fabsf(ux) * p.visc_coef;
         acc.ay += fabsf(ty) + fabsf(uy) * p.visc_coef;
@@ -274,7 +326,7 @@ __device__ __forceinline__ void force_pair(const DevParams& p, float dx, float d
 }
 
 // fallback walk straight from global memory (CTAs whose neighbourhood does not fit the staging buffer)
-template <bool DEBUG>
+template <bool DEBUG, bool EXACT>
 __device__ __forceinline__ void force_walk_global(const DevParams& p, const float2* __restrict__ pred,
                                                   const float2* __restrict__ vel, const float* __restrict__ rho,
                                                   const uint32_t (&a)[3], const uint32_t (&b)[3], uint32_t self, float px,
@@ -288,67 +340,73 @@ __device__ __forceinline__ void force_walk_global(const DevParams& p, const floa
             const float dx = fsub(q.x, px), dy = fsub(q.y, py);
             const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
             if (sq > p.h2) continue;  // compute.wgsl:202 (sqr_radius == h*h)
-            force_pair<DEBUG>(p, dx, dy, sq, vel[j], rho[j], vx, vy, pressure, rand_seed, acc);
+            force_pair<DEBUG, EXACT>(p, dx, dy, sq, vel[j], rho[j], vx, vy, pressure, rand_seed, acc);
         }
     }
 }
 
 // Staged walk, in two alternating warp-synchronous phases so that the expensive pair evaluation runs with
 // (nearly) all lanes active: only ~1/3 of the candidates in the 3x3 cells are within h, and evaluating
-// inside the candidate loop would execute the ~130-instruction pair body for a warp whenever ANY lane
-// accepts. Phase A scans candidates (cheap distance test) and appends accepted staging-buffer indices to
-// a per-thread list of up to FORCE_LIST entries, in visiting order; phase B evaluates the list in that
-// order. Visiting order, hence every fp32 sum, is unchanged.
+// inside the candidate loop would execute the whole pair body for a warp whenever ANY lane accepts.
+// Phase A scans candidates (cheap distance test) and appends accepted staging-buffer indices to a
+// per-thread list of up to FORCE_LIST entries, in visiting order; phase B evaluates the list in that
+// order. Visiting order, hence every fp32 sum, is unchanged. All shared accesses use explicit 32-bit
+// shared-window addresses so the loops carry no address arithmetic beyond one add.
 constexpr int FORCE_LIST = 16;
 
-template <bool DEBUG>
-__device__ __forceinline__ void force_walk_staged(const DevParams& p, const float2* __restrict__ sp,
-                                                  const float2* __restrict__ sv, const float* __restrict__ sr,
-                                                  uint16_t* __restrict__ list /* [FORCE_LIST][SPH_THREADS], this thread's column */,
+template <bool DEBUG, bool EXACT>
+__device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t sp_addr, uint32_t sv_addr, uint32_t sr_addr,
+                                                  uint32_t list_addr /* this thread's column of [FORCE_LIST][SPH_THREADS] u16 */,
                                                   const int (&base)[3], const uint32_t (&a)[3], const uint32_t (&b)[3],
                                                   uint32_t self, float px, float py, float vx, float vy, float pressure,
                                                   uint32_t& rand_seed, ForceAcc& acc) {
+    const uint32_t A1 = sp_addr + (a[1] - (uint32_t)base[1]) * 8u, E1 = sp_addr + (b[1] - (uint32_t)base[1]) * 8u;
+    const uint32_t A2 = sp_addr + (a[2] - (uint32_t)base[2]) * 8u, E2 = sp_addr + (b[2] - (uint32_t)base[2]) * 8u;
+    uint32_t addr = sp_addr + (a[0] - (uint32_t)base[0]) * 8u, end = sp_addr + (b[0] - (uint32_t)base[0]) * 8u;
+    const uint32_t self_addr = sp_addr + (self - (uint32_t)base[1]) * 8u;  // a particle lies in its own row's span
     int r = 0;
-    uint32_t j = a[0], end = b[0];
-    int off = base[0];
     bool more = true;
     while (__any_sync(0xffffffffu, more)) {
-        int cnt = 0;
+        uint32_t wr = list_addr;
+        const uint32_t wr_end = list_addr + FORCE_LIST * SPH_THREADS * 2u;
         // ---- phase A: scan ----
-        while (more && cnt < FORCE_LIST) {
-            if (j >= end) {  // next row span (constant indices keep a/b/base in registers)
-                if (r == 0) { j = a[1]; end = b[1]; off = base[1]; r = 1; }
-                else if (r == 1) { j = a[2]; end = b[2]; off = base[2]; r = 2; }
-                else { more = false; break; }
-                continue;
+        while (more) {
+            while (addr < end && wr < wr_end) {  // tight inner loop
+                const float2 q = lds_f2(addr);
+                const float dx = fsub(q.x, px), dy = fsub(q.y, py);
+                const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
+                if (addr != self_addr && !(sq > p.h2)) {  // compute.wgsl:195, :202
+                    sts_u16(wr, (addr - sp_addr) >> 3);
+                    wr += SPH_THREADS * 2u;
+                }
+                addr += 8u;
             }
-            const uint32_t sidx = j - (uint32_t)off;
-            const float2 q = sp[sidx];
-            const float dx = fsub(q.x, px), dy = fsub(q.y, py);
-            const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
-            if (j != self && !(sq > p.h2)) {  // compute.wgsl:195, :202
-                list[cnt * SPH_THREADS] = (uint16_t)sidx;
-                cnt++;
-            }
-            j++;
+            if (addr < end) break;  // list full: evaluate it, then resume this span
+            // next row span (constant indices keep a/b/base in registers)
+            if (r == 0) { addr = A1; end = E1; r = 1; }
+            else if (r == 1) { addr = A2; end = E2; r = 2; }
+            else more = false;
         }
         __syncwarp();
         // ---- phase B: evaluate ----
-        const int max_cnt = __reduce_max_sync(0xffffffffu, cnt);
-        for (int k = 0; k < max_cnt; k++) {
-            if (k < cnt) {
-                const uint32_t sidx = list[k * SPH_THREADS];
-                const float2 q = sp[sidx];
+        const uint32_t cnt_bytes = wr - list_addr;
+        const uint32_t max_bytes = __reduce_max_sync(0xffffffffu, cnt_bytes);
+        for (uint32_t k = 0; k < max_bytes; k += SPH_THREADS * 2u) {
+            if (k < cnt_bytes) {
+                const uint32_t sidx = lds_u16(list_addr + k);
+                const float2 q = lds_f2(sp_addr + sidx * 8u);
+                const float2 nv = lds_f2(sv_addr + sidx * 8u);
+                const float nd = lds_f(sr_addr + sidx * 4u);
                 const float dx = fsub(q.x, px), dy = fsub(q.y, py);
                 const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
-                force_pair<DEBUG>(p, dx, dy, sq, sv[sidx], sr[sidx], vx, vy, pressure, rand_seed, acc);
+                force_pair<DEBUG, EXACT>(p, dx, dy, sq, nv, nd, vx, vy, pressure, rand_seed, acc);
             }
         }
         __syncwarp();
     }
 }
 
-template <bool DEBUG>
+template <bool DEBUG, bool EXACT>
 __global__ void __launch_bounds__(SPH_THREADS)
 k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const float2* __restrict__ pred_s,
                   const float2* __restrict__ vel_s, const float* __restrict__ rho, const uint32_t* __restrict__ keys,
@@ -394,10 +452,10 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
         mbar_wait(&s_bar, 0);
         int base[3];
         thread_bases(s_plan, valid ? cy : s_plan.row_first, base);
-        force_walk_staged<DEBUG>(p, s_pred, s_vel, s_rho, s_list + threadIdx.x, base, a, b, i, pred.x, pred.y, vel.x, vel.y,
-                                 pressure, rand_seed, acc);
+        force_walk_staged<DEBUG, EXACT>(p, smem_u32_pinned(s_pred), smem_u32_pinned(s_vel), smem_u32_pinned(s_rho), smem_u32_pinned(s_list + threadIdx.x),
+                                        base, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
     } else {
-        force_walk_global<DEBUG>(p, pred_s, vel_s, rho, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
+        force_walk_global<DEBUG, EXACT>(p, pred_s, vel_s, rho, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
     }
     if (!valid) return;
 

@@ -41,6 +41,7 @@ struct Sim {
     FluidParticle* aos_stage = nullptr;
     float2 *dbg_accel = nullptr, *dbg_abs = nullptr;
     bool debug_force = false;
+    bool exact_math = true;   // FLUID_MATH_EXACT / FLUID_MATH_FAST
 
     uint32_t *jfa_a = nullptr, *jfa_b = nullptr;  // packed seed ping-pong for fluid_sim_jfa_from_particles
     size_t jfa_pixels = 0;

@@ -135,6 +135,16 @@ class FluidSimulation:
         ts = settings.to_c()
         _lib.check(self._lib.fluid_sim_tick_hash_sort_only(self._h, C.byref(ts)))
 
+    MATH_EXACT, MATH_FAST = 0, 1
+
+    @property
+    def math_mode(self) -> int:
+        return int(self._lib.fluid_sim_get_math_mode(self._h))
+
+    @math_mode.setter
+    def math_mode(self, mode: int):
+        _lib.check(self._lib.fluid_sim_set_math_mode(self._h, int(mode)))
+
     def sync(self):
         _lib.check(self._lib.fluid_sim_sync(self._h))
 

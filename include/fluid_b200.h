@@ -134,6 +134,16 @@ int fluid_sim_sync(FluidSim* sim);
 uint32_t fluid_sim_tick_count(const FluidSim* sim);
 int fluid_sim_set_tick_count(FluidSim* sim, uint32_t tick);
 
+/* Arithmetic of the force pass (the reference's WGSL leaves division / sqrt accuracy to the driver: 2.5 ulp).
+ * FLUID_MATH_EXACT (default): IEEE-rounded operations in the shader's order, bit-identical to the CPU restatement.
+ * FLUID_MATH_FAST: hardware reciprocal / rsqrt and FMA contraction in the pressure+viscosity pair terms; keys,
+ * sorted order, cell tables, predicted positions and densities are unchanged, velocity/position agree with
+ * EXACT within 1e-5 (relative to sum|terms|). */
+#define FLUID_MATH_EXACT 0
+#define FLUID_MATH_FAST 1
+int fluid_sim_set_math_mode(FluidSim* sim, int mode);
+int fluid_sim_get_math_mode(const FluidSim* sim);
+
 /* BASELINE.json config 2: spatial hash + key sort + cell-start table only
  * (reference passes K1..K4: compute.wgsl:8-56, sort.wgsl:27-51). Increments tick. */
 int fluid_sim_tick_hash_sort_only(FluidSim* sim, const FluidTickSettings* tick);

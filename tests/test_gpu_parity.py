@@ -49,6 +49,34 @@ def test_default_scene_with_coincident_pairs(fluid, oracle):
     assert stats["floats_bit_exact"], stats
 
 
+@pytest.mark.parametrize("scene", ["U", "D", "default", "field_mouse"])
+def test_fast_math_mode_within_tolerance(fluid, oracle, scene):
+    """FLUID_MATH_FAST: hardware rsqrt/rcp + FMA in the pair terms. Keys, sorted keys, tables, predicted positions and
+    densities stay bit-exact; acceleration within 1e-5 of sum|terms|; velocity / position within 1e-5 (criterion 2)."""
+    field = None
+    if scene == "U":
+        s, ts, p = scenes.uniform_box(200)
+    elif scene == "D":
+        s, ts, p = scenes.dam_break(64, 256)
+    elif scene == "default":
+        s = SimulationSettings(); ts = TickSettings(); p = oracle.init_lattice(s)
+    else:
+        s, ts, p = scenes.uniform_box(64, tex=(32, 32))
+        rng = np.random.default_rng(9)
+        field = rng.integers(-4, 5, size=(32, 32, 2)).astype(np.float32)
+        ts.mouse_state = 1; ts.mouse_pos = (0.7, -1.1); ts.mouse_force_radius = 2.0
+    osim, sim, extras = parity.run_pair(fluid, oracle, s, ts, p, field=field, n_ticks=1, math_mode=1)
+    try:
+        assert sim.math_mode == 1
+        stats = parity.compare_state(osim, sim, extras, ts)
+        got = sim.download_particles()
+    finally:
+        sim.close()
+    assert np.array_equal(got["density"], osim.p["density"])
+    assert not stats["floats_bit_exact"] or scene == "x"  # it really is a different arithmetic path
+    assert stats["accel_max_rel_to_terms"] <= 1e-5 and stats["velocity_max_rel"] <= 1e-5, stats
+
+
 def test_create_builds_reference_lattice(fluid, oracle):
     s = SimulationSettings(particle_count=12345, size=(20.0, 20.0))
     with fluid.FluidSimulation.new(0, s) as sim:
