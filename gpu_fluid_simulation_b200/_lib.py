@@ -54,6 +54,13 @@ class DeviceView(C.Structure):
                 ("force_field", C.c_void_p)]
 
 
+class SlabView(C.Structure):
+    _fields_ = [("n", C.c_uint32), ("pad", C.c_uint32), ("capacity", C.c_uint32), ("emig_cap", C.c_uint32),
+                ("pos_state", C.c_void_p), ("vel_state", C.c_void_p), ("pos_sorted", C.c_void_p),
+                ("pred_sorted", C.c_void_p), ("vel_sorted", C.c_void_p), ("rho", C.c_void_p), ("keys_ext", C.c_void_p),
+                ("emig_list", C.c_void_p), ("emig_count", C.c_void_p), ("meta", C.c_void_p), ("start_indices", C.c_void_p)]
+
+
 _P = C.c_void_p
 _u32 = C.c_uint32
 _i = C.c_int
@@ -94,6 +101,12 @@ PROTOTYPES = {
     "fluid_sim_launch_count": (C.c_uint64, [_P]),
     "fluid_sim_reserve": (_i, [_P, _u32]),
     "fluid_sim_set_particle_count": (_i, [_P, _u32]),
+    "fluid_slab_configure": (_i, [_P, _i, _i, _P, _u32, _u32, _u32]),
+    "fluid_slab_view": (_i, [_P, C.POINTER(SlabView)]),
+    "fluid_slab_begin_tick": (_i, [_P, C.POINTER(TickSettingsC)]),
+    "fluid_slab_sort": (_i, [_P, _u32, _u32, _u32]),
+    "fluid_slab_cells_density": (_i, [_P, _u32, _u32, _u32, _u32, _u32]),
+    "fluid_slab_force": (_i, [_P]),
     "fluid_jfa_run": (_i, [_P, _u32, _u32, _P, _i]),
     "fluid_jfa_pass": (_i, [_P, _u32, _u32, _u32, _P, _i]),
     "fluid_jfa_seed_from_mask": (_i, [_P, _u32, _u32, _P, _i]),

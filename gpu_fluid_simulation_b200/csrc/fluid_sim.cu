@@ -184,6 +184,20 @@ void Sim::mark(const char* name) {
     n_marks++;
 }
 
+void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, float2* vel_out) {
+    float2* da = s->debug_force ? s->dbg_accel : nullptr;
+    float2* db = s->debug_force ? s->dbg_abs : nullptr;
+    const uint32_t* keys = s->slab ? s->keys_ext : s->keys_sorted;
+#define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                     \
+    k_force_integrate<DBG, EX><<<blocks, SPH_THREADS, 0, s->stream>>>(p, s->pos_s, s->pred_s, s->vel_s, s->rho, keys,   \
+                                                                      s->cell_lb, s->quirk, s->force_field,             \
+                                                                      s->d_frame_time, pos_out, vel_out, da, db)
+    if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
+    else { if (s->exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
+#undef FLUID_LAUNCH_FORCE
+    s->launches++;
+}
+
 template <int PASSES>
 static void launch_hash(Sim* s, const DevParams& p, uint32_t* hist) {
     const uint32_t pairs = (p.n + 1) / 2;
@@ -258,17 +272,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     k_density<<<sblocks, SPH_THREADS, 0, stream>>>(p, pred_s, keys_sorted, cell_lb, quirk, rho);
     launches++;
     mark("density");
-    {
-        float2* da = debug_force ? dbg_accel : nullptr;
-        float2* db = debug_force ? dbg_abs : nullptr;
-#define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                        \
-    k_force_integrate<DBG, EX><<<sblocks, SPH_THREADS, 0, stream>>>(p, pos_s, pred_s, vel_s, rho, keys_sorted, cell_lb, quirk, \
-                                                                    force_field, d_frame_time, pos_a, vel_a, da, db)
-        if (debug_force) { if (exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
-        else { if (exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
-#undef FLUID_LAUNCH_FORCE
-    }
-    launches++;
+    launch_force(this, p, sblocks, pos_a, vel_a);
     mark("force+integrate");
     if (timing) { marks_per_tick = n_marks; timed_ticks++; }
     FLUID_CUDA(cudaGetLastError());
@@ -374,7 +378,7 @@ void fluid_sim_destroy(FluidSim* h) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
                     s->idx_b, s->sort_scratch, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
-                    s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b};
+                    s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta};
     for (void* b : bufs) if (b) cudaFree(b);
     for (auto& row : s->mark_events) for (auto& e : row) if (e) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);
@@ -387,14 +391,18 @@ void fluid_sim_destroy(FluidSim* h) {
     Sim* s = reinterpret_cast<Sim*>(h);                                  \
     FLUID_CUDA(cudaSetDevice(s->device));
 
+#define NOT_SLAB(s) if ((s)->slab) return invalid("handle is in slab mode: drive it with the fluid_slab_* phases")
+
 int fluid_sim_tick(FluidSim* h, const FluidTickSettings* t) {
     SIM_OR_FAIL(h);
+    NOT_SLAB(s);
     if (!t) return invalid("fluid_sim_tick: null settings");
     return s->enqueue_tick(*t, false);
 }
 int fluid_sim_tick_n(FluidSim* h, const FluidTickSettings* t, uint32_t count) {
     SIM_OR_FAIL(h);
     if (!t) return invalid("fluid_sim_tick_n: null settings");
+    NOT_SLAB(s);
     for (uint32_t k = 0; k < count; k++) {
         int rc = s->enqueue_tick(*t, false);
         if (rc != FLUID_OK) return rc;
@@ -404,6 +412,7 @@ int fluid_sim_tick_n(FluidSim* h, const FluidTickSettings* t, uint32_t count) {
 int fluid_sim_tick_hash_sort_only(FluidSim* h, const FluidTickSettings* t) {
     SIM_OR_FAIL(h);
     if (!t) return invalid("fluid_sim_tick_hash_sort_only: null settings");
+    NOT_SLAB(s);
     return s->enqueue_tick(*t, true);
 }
 int fluid_sim_sync(FluidSim* h) {
@@ -434,7 +443,9 @@ int fluid_sim_download_particles(FluidSim* h, FluidParticle* dst) {
     if (!dst) return invalid("fluid_sim_download_particles: null destination");
     int rc = ensure_stage(s);
     if (rc != FLUID_OK) return rc;
-    k_soa_to_aos<<<(s->n + 255) / 256, 256, 0, s->stream>>>(s->aos_stage, s->n, s->pos_a, s->pred_s, s->vel_a, s->rho, s->keys_sorted);
+    if (s->n == 0) return FLUID_OK;
+    k_soa_to_aos<<<(s->n + 255) / 256, 256, 0, s->stream>>>(s->aos_stage, s->n, s->pos_a + s->state_off, s->pred_s + s->sorted_off,
+                                                          s->vel_a + s->state_off, s->rho + s->sorted_off, s->keys_view());
     s->launches++;
     FLUID_CUDA(cudaMemcpyAsync(dst, s->aos_stage, (size_t)s->n * sizeof(FluidParticle), cudaMemcpyDeviceToHost, s->stream));
     FLUID_CUDA(cudaStreamSynchronize(s->stream));
@@ -446,7 +457,9 @@ int fluid_sim_upload_particles(FluidSim* h, const FluidParticle* src) {
     int rc = ensure_stage(s);
     if (rc != FLUID_OK) return rc;
     FLUID_CUDA(cudaMemcpyAsync(s->aos_stage, src, (size_t)s->n * sizeof(FluidParticle), cudaMemcpyHostToDevice, s->stream));
-    k_aos_to_soa<<<(s->n + 255) / 256, 256, 0, s->stream>>>(s->aos_stage, s->n, s->pos_a, s->pred_s, s->vel_a, s->rho, s->keys_sorted);
+    if (s->n == 0) return FLUID_OK;
+    k_aos_to_soa<<<(s->n + 255) / 256, 256, 0, s->stream>>>(s->aos_stage, s->n, s->pos_a + s->state_off, s->pred_s + s->sorted_off,
+                                                          s->vel_a + s->state_off, s->rho + s->sorted_off, s->keys_view());
     s->launches++;
     FLUID_CUDA(cudaGetLastError());
     // the source buffer may be pageable: the copy above is then already complete on return; for pinned
@@ -524,8 +537,8 @@ int fluid_sim_device_view(FluidSim* h, FluidSimDeviceView* out) {
     SIM_OR_FAIL(h);
     if (!out) return invalid("null argument");
     out->particle_count = s->n; out->capacity = s->capacity;
-    out->position = s->pos_a; out->predicted_position = s->pred_s; out->velocity = s->vel_a;
-    out->density = s->rho; out->grid = s->keys_sorted;
+    out->position = s->pos_a + s->state_off; out->predicted_position = s->pred_s + s->sorted_off;
+    out->velocity = s->vel_a + s->state_off; out->density = s->rho + s->sorted_off; out->grid = s->keys_view();
     out->start_indices = s->start_indices; out->cell_lower_bound = s->cell_lb; out->force_field = s->force_field;
     return FLUID_OK;
 }
@@ -572,6 +585,7 @@ int fluid_sim_get_math_mode(const FluidSim* h) {
 
 int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
     SIM_OR_FAIL(h);
+    NOT_SLAB(s);
     if (capacity <= s->capacity) return FLUID_OK;
     // contents are preserved through a host-free device round trip of the live arrays
     const uint32_t n = s->n;
@@ -600,9 +614,16 @@ int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
 }
 int fluid_sim_set_particle_count(FluidSim* h, uint32_t n) {
     SIM_OR_FAIL(h);
+    if (s->slab) {
+        if (n > s->slab_capacity) return invalid("fluid_sim_set_particle_count: n exceeds the slab capacity");
+        s->n = n;
+        return FLUID_OK;
+    }
     if (n < 2 || n > s->capacity) return invalid("fluid_sim_set_particle_count: need 2 <= n <= capacity");
     s->n = n;
     return FLUID_OK;
 }
 
 }  // extern "C"
+
+#include "slab.inl"

@@ -1,0 +1,158 @@
+// kernels_slab.cuh — the extra passes of slab (multi-GPU) mode. SURVEY.md §8(e).
+//
+// The domain is cut into bands of grid rows, one band per rank. Keys stay GLOBAL (funcs.wgsl:216-218), so
+// the concatenation of the ranks' sorted key arrays is the single-GPU sorted key array, and
+// global_start[c] = local_start[c] + (number of particles on lower ranks).
+//
+// Per tick and rank:
+//   1. k_slab_key_hist    keys of the particles the rank held after the last tick ("natives"); a particle whose
+//                         predicted position left the band is an emigrant: it gets the sentinel key (sorts last,
+//                         dropped after the sort) and is appended to an emigrant list (destination rank, index)
+//   2. [exchange]         emigrants' (pos, vel) go to their new owner. Immigrants from lower ranks are placed
+//                         BEFORE the natives and immigrants from higher ranks AFTER them, in source order, so the
+//                         stable sort reproduces the single-GPU tie order exactly
+//   3. k_slab_key_hist    keys of the immigrants (no emigrant detection); then the ordinary onesweep passes
+//   4. k_slab_gather      payload into key order, at an offset that leaves room for the halo row below
+//   5. [exchange]         first / last grid row of (pred, vel) to the lower / upper neighbour -> halo rows
+//   6. k_slab_halo_keys, k_slab_build_cells   keys of halo particles; cell tables over [halo | owned | halo]
+//   7. k_density over the owned range; [exchange] rho of the same rows; k_force_integrate over the owned range
+#pragma once
+#include "common.cuh"
+#include "kernels_cells.cuh"
+#include "kernels_hash.cuh"
+#include "slab_rows.h"
+
+namespace fluid {
+
+// 1 particle per thread (the range may start at an odd index, so no float4 loads here)
+template <int PASSES>
+__global__ void __launch_bounds__(HASH_THREADS)
+k_slab_key_hist(const DevParams p, const float2* __restrict__ pos, const float2* __restrict__ vel, uint32_t count,
+                uint32_t* __restrict__ keys, uint32_t* __restrict__ g_hist, const SlabRows rows, int detect_emigrants,
+                uint32_t list_index_base, unsigned long long* __restrict__ emig_list, uint32_t* __restrict__ emig_count,
+                uint32_t emig_cap, uint32_t sentinel_key, uint32_t* __restrict__ frame_time) {
+    __shared__ uint32_t s_hist[PASSES * RADIX];
+    for (int i = threadIdx.x; i < PASSES * RADIX; i += HASH_THREADS) s_hist[i] = 0;
+    __syncthreads();
+    if (frame_time && blockIdx.x == 0 && threadIdx.x == 0) *frame_time += 1u;
+    const uint32_t stride = gridDim.x * HASH_THREADS;
+    const uint32_t end = (count + 31u) & ~31u;
+    const uint32_t row_lo = rows.bounds[rows.rank], row_hi = rows.bounds[rows.rank + 1];
+    for (uint32_t i = blockIdx.x * HASH_THREADS + threadIdx.x; i < end; i += stride) {
+        const bool v = i < count;
+        uint32_t k = 0;
+        if (v) {
+            k = cell_key(p, predict_position(p, __ldg(pos + i), __ldg(vel + i)));
+            if (detect_emigrants) {
+                const uint32_t row = k / p.grid_w;
+                if (row < row_lo || row >= row_hi) {
+                    int dest = 0;
+#pragma unroll 1
+                    for (int r = 0; r < rows.world; r++) if (row >= rows.bounds[r]) dest = r;
+                    const uint32_t slot = atomicAdd(emig_count, 1u);
+                    if (slot < emig_cap) emig_list[slot] = ((unsigned long long)dest << 32) | (unsigned long long)(list_index_base + i);
+                    k = sentinel_key;
+                }
+            }
+            keys[i] = k;
+        }
+#pragma unroll
+        for (int q = 0; q < PASSES; q++) hist_add(s_hist + q * RADIX, (k >> (q * RADIX_BITS)) & (RADIX - 1), v);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < PASSES * RADIX; i += HASH_THREADS) {
+        uint32_t c = s_hist[i];
+        if (c) atomicAdd(g_hist + i, c);
+    }
+}
+
+// payload + keys into key order at `own_begin`
+__global__ void __launch_bounds__(GATHER_THREADS)
+k_slab_gather(const DevParams p, const uint32_t* __restrict__ sorted_keys, const uint32_t* __restrict__ sorted_idx,
+              const float2* __restrict__ pos_in, const float2* __restrict__ vel_in, float2* __restrict__ pos_s,
+              float2* __restrict__ pred_s, float2* __restrict__ vel_s, uint32_t* __restrict__ keys_ext) {
+    const uint32_t i = blockIdx.x * GATHER_THREADS + threadIdx.x;
+    if (i >= p.n) return;
+    const uint32_t src = __ldg(sorted_idx + i);
+    const float2 ps = __ldg(pos_in + src), vs = __ldg(vel_in + src);
+    const uint32_t o = p.own_begin + i;
+    pos_s[o] = ps;
+    vel_s[o] = vs;
+    pred_s[o] = predict_position(p, ps, vs);
+    keys_ext[o] = __ldg(sorted_keys + i);
+}
+
+// keys of received halo particles from their predicted positions (same arithmetic as the hash pass)
+__global__ void k_slab_halo_keys(const DevParams p, const float2* __restrict__ pred_s, uint32_t* __restrict__ keys_ext,
+                                 uint32_t below_begin, uint32_t below_count, uint32_t above_begin, uint32_t above_count) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t i;
+    if (t < below_count) i = below_begin + t;
+    else if (t < below_count + above_count) i = above_begin + (t - below_count);
+    else return;
+    keys_ext[i] = cell_key(p, __ldg(pred_s + i));
+}
+
+// cell tables over the extended range. start_indices holds GLOBAL sorted indices for owned cells
+// (compute.wgsl:45-56: global particle 0 writes nothing); cell_lb holds local (extended) indices.
+__global__ void __launch_bounds__(GATHER_THREADS)
+k_slab_build_cells(const DevParams p, const uint32_t* __restrict__ keys_ext, uint32_t* __restrict__ start_indices,
+                   uint32_t* __restrict__ cell_lb, uint32_t* __restrict__ quirk, uint32_t quirk_c0, uint32_t quirk_stale) {
+    const uint32_t i = p.ext_begin + blockIdx.x * GATHER_THREADS + threadIdx.x;
+    const bool valid = i < p.ext_end;
+    uint32_t gap_begin = 0, gap_end = 0, gap_value = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { quirk[0] = quirk_c0; quirk[1] = quirk_stale; }
+    if (valid) {
+        const uint32_t kc = min(__ldg(keys_ext + i), p.num_cells - 1u);
+        const bool owned = i >= p.own_begin && i < p.own_begin + p.n;
+        const uint32_t gidx = i - p.own_begin + p.global_offset;
+        if (i == p.ext_begin) {
+            gap_begin = 0; gap_end = kc + 1u; gap_value = p.ext_begin;
+            if (owned && gidx > 0u) start_indices[kc] = gidx;  // previous global particle lives on a lower rank, in another row
+        } else {
+            const uint32_t kp = min(__ldg(keys_ext + i - 1), p.num_cells - 1u);
+            if (kc != kp) {
+                if (owned && gidx > 0u) start_indices[kc] = gidx;
+                gap_begin = kp + 1u; gap_end = kc + 1u; gap_value = i;
+            }
+        }
+    }
+    warp_fill_gaps(cell_lb, gap_begin, gap_end, gap_value);
+    uint32_t tb = 0, te = 0;
+    if (valid && i == p.ext_end - 1u) {
+        tb = min(__ldg(keys_ext + i), p.num_cells - 1u) + 1u;
+        te = p.num_cells + 1u;
+    }
+    if (__any_sync(0xffffffffu, te > tb)) warp_fill_gaps(cell_lb, tb, te, p.ext_end);
+}
+// an empty extended range still needs a valid (all-empty) table
+__global__ void k_slab_fill_table(uint32_t* __restrict__ cell_lb, uint32_t count, uint32_t value) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) cell_lb[i] = value;
+}
+
+// meta[0] = owned particles in the band's first grid row, meta[1] = in its last grid row,
+// meta[2] = key of the first owned particle, meta[3] = this rank's start_indices entry for that key
+__global__ void k_slab_meta(const uint32_t* __restrict__ keys_owned, uint32_t n, uint32_t grid_w, uint32_t row_first,
+                            uint32_t row_last, const uint32_t* __restrict__ start_indices, uint32_t num_cells,
+                            uint32_t* __restrict__ meta) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    // lower_bound(keys, (row_first + 1) * grid_w) and lower_bound(keys, row_last * grid_w)
+    uint32_t targets[2] = {(row_first + 1u) * grid_w, row_last * grid_w};
+    uint32_t res[2];
+    for (int t = 0; t < 2; t++) {
+        uint32_t lo = 0, hi = n;
+        while (lo < hi) {
+            uint32_t mid = (lo + hi) >> 1;
+            if (keys_owned[mid] < targets[t]) lo = mid + 1; else hi = mid;
+        }
+        res[t] = lo;
+    }
+    meta[0] = res[0];
+    meta[1] = n - res[1];
+    const uint32_t k0 = n ? min(keys_owned[0], num_cells - 1u) : 0xffffffffu;
+    meta[2] = k0;
+    meta[3] = n ? start_indices[k0] : 0u;
+}
+
+}  // namespace fluid

@@ -195,8 +195,9 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
     __shared__ __align__(128) float2 s_pred[SPH_CAP];
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
-    const uint32_t i0 = blockIdx.x * SPH_THREADS;
-    const uint32_t i1 = min(i0 + SPH_THREADS, p.n);
+    // slab mode: owned particles are [own_begin, own_begin + n) of arrays that also hold halo rows on both sides
+    const uint32_t i0 = p.own_begin + blockIdx.x * SPH_THREADS;
+    const uint32_t i1 = min(i0 + SPH_THREADS, p.own_begin + p.n);
     if (threadIdx.x == 0) {
         mbar_init(&s_bar, 1);
         mbar_fence_init();
@@ -206,7 +207,7 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
         plan_and_stage<1>(p, i0, i1, keys, lb, arrays, smem, eb, &s_bar, &s_plan);
     }
     const uint32_t i = i0 + threadIdx.x;
-    const bool valid = i < p.n;
+    const bool valid = i < p.own_begin + p.n;
     uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
     float2 me = make_float2(0.f, 0.f);
     uint32_t cy = 0;
@@ -420,8 +421,9 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     __shared__ uint16_t s_list[FORCE_LIST * SPH_THREADS];
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
-    const uint32_t i0 = blockIdx.x * SPH_THREADS;
-    const uint32_t i1 = min(i0 + SPH_THREADS, p.n);
+    // slab mode: owned particles are [own_begin, own_begin + n) of arrays that also hold halo rows on both sides
+    const uint32_t i0 = p.own_begin + blockIdx.x * SPH_THREADS;
+    const uint32_t i1 = min(i0 + SPH_THREADS, p.own_begin + p.n);
     if (threadIdx.x == 0) {
         mbar_init(&s_bar, 1);
         mbar_fence_init();
@@ -431,7 +433,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
         plan_and_stage<3>(p, i0, i1, keys, lb, arrays, smem, eb, &s_bar, &s_plan);
     }
     const uint32_t i = i0 + threadIdx.x;
-    const bool valid = i < p.n;
+    const bool valid = i < p.own_begin + p.n;
     uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
     float2 pos = make_float2(0.f, 0.f), pred = pos, vel = pos;
     float dens = 1.0f;
@@ -444,7 +446,8 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
         dens = __ldg(rho + i);
     }
     const uint32_t ft = __ldg(frame_time);
-    uint32_t rand_seed = i * 12u + ft * 69u;  // compute.wgsl:161
+    const uint32_t out_i = i - p.own_begin;                      // index in the (halo-free) state arrays
+    uint32_t rand_seed = (out_i + p.global_offset) * 12u + ft * 69u;  // compute.wgsl:161 (global sorted index)
     const float pressure = fmul(p.pressure_constant, fsub(dens, p.rest_density));
     ForceAcc acc = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     __syncthreads();
@@ -463,8 +466,8 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     const float fvx = fmul(acc.vx, p.visc_coef), fvy = fmul(acc.vy, p.visc_coef);
     const float ax = fadd(acc.px, fvx), ay = fadd(acc.py, fvy);
     if (DEBUG) {
-        dbg_accel[i] = make_float2(ax, ay);
-        dbg_abs[i] = make_float2(acc.ax, acc.ay);
+        dbg_accel[out_i] = make_float2(ax, ay);
+        dbg_abs[out_i] = make_float2(acc.ax, acc.ay);
     }
     float vx = fadd(vel.x, fmul(fdiv(ax, dens), p.dt));
     float vy = fadd(vel.y, fmul(fdiv(ay, dens), p.dt));
@@ -513,8 +516,8 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     // compute.wgsl:143-153 walls
     if (fabsf(nx) > p.half_x) { nx = fmul(p.half_x, fsign(nx)); vx = fmul(vx, p.neg_damping); }
     if (fabsf(ny) > p.half_y) { ny = fmul(p.half_y, fsign(ny)); vy = fmul(vy, p.neg_damping); }
-    pos_out[i] = make_float2(nx, ny);
-    vel_out[i] = make_float2(vx, vy);
+    pos_out[out_i] = make_float2(nx, ny);
+    vel_out[out_i] = make_float2(vx, vy);
 }
 
 }  // namespace fluid

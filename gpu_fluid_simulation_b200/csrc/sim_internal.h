@@ -1,6 +1,7 @@
 // sim_internal.h — the state behind the opaque FluidSim handle.
 #pragma once
 #include "common.cuh"
+#include "slab_rows.h"
 
 namespace fluid {
 
@@ -43,6 +44,19 @@ struct Sim {
     bool debug_force = false;
     bool exact_math = true;   // FLUID_MATH_EXACT / FLUID_MATH_FAST
 
+    // slab (multi-GPU) mode, kernels_slab.cuh / slab.inl
+    bool slab = false;
+    uint32_t slab_pad = 0, slab_capacity = 0;
+    uint32_t state_off = 0;    // index of the first native in pos_a / vel_a / keys_u
+    uint32_t sorted_off = 0;   // index of the first owned particle in pos_s / pred_s / vel_s / rho / keys_ext
+    SlabRows slab_rows{};
+    uint32_t* keys_ext = nullptr;              // keys of [halo | owned | halo]
+    unsigned long long* emig_list = nullptr;   // (destination rank << 32) | index in the state arrays
+    uint32_t* emig_count = nullptr;
+    uint32_t emig_cap = 0;
+    uint32_t* slab_meta = nullptr;
+    DevParams slab_params{};
+
     uint32_t *jfa_a = nullptr, *jfa_b = nullptr;  // packed seed ping-pong for fluid_sim_jfa_from_particles
     size_t jfa_pixels = 0;
 
@@ -60,6 +74,7 @@ struct Sim {
     DevParams make_params(const FluidSimUniform& u) const;
     void mark(const char* name);
     int enqueue_tick(const FluidTickSettings& t, bool hash_sort_only);
+    uint32_t* keys_view() const { return slab ? keys_ext + sorted_off : keys_sorted; }
 };
 
 }  // namespace fluid

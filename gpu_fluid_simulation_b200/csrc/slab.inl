@@ -1,0 +1,213 @@
+// slab.inl — C ABI of slab (multi-GPU) mode: one FluidSim handle per rank owns a band of grid rows.
+// The exchanges themselves (NCCL over NVLink) are driven from the host language through
+// torch.distributed on views of this handle's device arrays (gpu_fluid_simulation_b200/slab.py);
+// this file holds the device passes in between. See kernels_slab.cuh for the per-tick sequence.
+// (textually included at the end of fluid_sim.cu: one translation unit, so the kernels are defined once)
+#include "kernels_slab.cuh"
+
+#define SLAB_OR_FAIL(h)                                                                   \
+    if (!(h)) { set_error("null FluidSim handle"); return FLUID_ERR_INVALID_ARGUMENT; }   \
+    Sim* s = reinterpret_cast<Sim*>(h);                                                   \
+    FLUID_CUDA(cudaSetDevice(s->device));                                                 \
+    if (!s->slab) { set_error("handle is not in slab mode (call fluid_slab_configure)"); return FLUID_ERR_INVALID_ARGUMENT; }
+
+template <int PASSES>
+static void launch_slab_hash(Sim* s, const DevParams& p, uint32_t begin, uint32_t count, int detect, uint32_t* frame_time) {
+    if (count == 0 && !frame_time) return;
+    uint32_t blocks = (count + HASH_THREADS - 1) / HASH_THREADS;
+    if (blocks == 0) blocks = 1;
+    const uint32_t max_blocks = (uint32_t)s->num_sms * 8u;
+    if (blocks > max_blocks) blocks = max_blocks;
+    k_slab_key_hist<PASSES><<<blocks, HASH_THREADS, 0, s->stream>>>(
+        p, s->pos_a + begin, s->vel_a + begin, count, s->keys_u + begin, s->sort_scratch, s->slab_rows, detect,
+        begin, s->emig_list, s->emig_count, s->emig_cap, s->num_cells, frame_time);
+    s->launches++;
+}
+static void slab_hash(Sim* s, const DevParams& p, uint32_t begin, uint32_t count, int detect, uint32_t* frame_time) {
+    switch (s->sort_passes) {
+        case 1: launch_slab_hash<1>(s, p, begin, count, detect, frame_time); break;
+        case 2: launch_slab_hash<2>(s, p, begin, count, detect, frame_time); break;
+        case 3: launch_slab_hash<3>(s, p, begin, count, detect, frame_time); break;
+        default: launch_slab_hash<4>(s, p, begin, count, detect, frame_time); break;
+    }
+}
+
+extern "C" {
+
+int fluid_slab_configure(FluidSim* h, int rank, int world, const uint32_t* row_bounds, uint32_t capacity, uint32_t pad,
+                         uint32_t emig_cap) {
+    if (!h || !row_bounds) { set_error("fluid_slab_configure: null argument"); return FLUID_ERR_INVALID_ARGUMENT; }
+    Sim* s = reinterpret_cast<Sim*>(h);
+    FLUID_CUDA(cudaSetDevice(s->device));
+    if (world < 1 || world > SLAB_MAX_RANKS || rank < 0 || rank >= world) { set_error("fluid_slab_configure: bad rank/world"); return FLUID_ERR_INVALID_ARGUMENT; }
+    for (int r = 0; r < world; r++)
+        if (row_bounds[r] > row_bounds[r + 1]) { set_error("fluid_slab_configure: row bounds must be non-decreasing"); return FLUID_ERR_INVALID_ARGUMENT; }
+    pad = (pad + 63u) & ~63u;
+    if (capacity < 2 || emig_cap == 0) { set_error("fluid_slab_configure: bad capacity"); return FLUID_ERR_INVALID_ARGUMENT; }
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    const bool dbg = s->debug_force;
+    int rc = s->alloc(capacity + 2u * pad);  // contents dropped: the caller uploads its band afterwards
+    if (rc != FLUID_OK) return rc;
+    if (s->keys_ext) cudaFree(s->keys_ext);
+    if (s->emig_list) cudaFree(s->emig_list);
+    if (s->slab_meta) cudaFree(s->slab_meta);
+    FLUID_CUDA(cudaMalloc(&s->keys_ext, ((size_t)capacity + 2u * pad + 64) * 4));
+    FLUID_CUDA(cudaMemsetAsync(s->keys_ext, 0, ((size_t)capacity + 2u * pad + 64) * 4, s->stream));
+    FLUID_CUDA(cudaMalloc(&s->emig_list, (size_t)emig_cap * 8));
+    FLUID_CUDA(cudaMalloc(&s->slab_meta, 64));
+    FLUID_CUDA(cudaMemsetAsync(s->slab_meta, 0, 64, s->stream));
+    s->emig_count = s->slab_meta + 8;  // meta words 0..3, emigrant counter at word 8
+    s->emig_cap = emig_cap;
+    s->slab = true;
+    s->slab_pad = pad;
+    s->slab_capacity = capacity;
+    memset(&s->slab_rows, 0, sizeof s->slab_rows);
+    for (int r = 0; r <= world; r++) s->slab_rows.bounds[r] = row_bounds[r];
+    s->slab_rows.world = world;
+    s->slab_rows.rank = rank;
+    s->state_off = pad;
+    s->sorted_off = pad;
+    s->n = 0;
+    // the sentinel key num_cells must be sortable: one more key value than a single GPU needs
+    uint32_t bits = 0;
+    while (bits < 32 && (s->num_cells >> bits) != 0) bits++;
+    s->sort_passes = (bits + RADIX_BITS - 1) / RADIX_BITS;
+    if (s->sort_passes < 1) s->sort_passes = 1;
+    if (dbg) {
+        FLUID_CUDA(cudaMalloc(&s->dbg_accel, ((size_t)capacity + 64) * 8));
+        FLUID_CUDA(cudaMalloc(&s->dbg_abs, ((size_t)capacity + 64) * 8));
+        s->debug_force = true;
+    }
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    return FLUID_OK;
+}
+
+int fluid_slab_view(FluidSim* h, FluidSlabView* out) {
+    SLAB_OR_FAIL(h);
+    if (!out) { set_error("null argument"); return FLUID_ERR_INVALID_ARGUMENT; }
+    out->n = s->n; out->pad = s->slab_pad; out->capacity = s->slab_capacity; out->emig_cap = s->emig_cap;
+    out->pos_state = s->pos_a; out->vel_state = s->vel_a;
+    out->pos_sorted = s->pos_s; out->pred_sorted = s->pred_s; out->vel_sorted = s->vel_s; out->rho = s->rho;
+    out->keys_ext = s->keys_ext; out->emig_list = s->emig_list; out->emig_count = s->emig_count; out->meta = s->slab_meta;
+    out->start_indices = s->start_indices;
+    return FLUID_OK;
+}
+
+// phase 1: tick += 1, uniform, clear sort scratch + emigrant list, keys of the natives with emigrant detection
+int fluid_slab_begin_tick(FluidSim* h, const FluidTickSettings* t) {
+    SLAB_OR_FAIL(h);
+    if (!t) { set_error("null settings"); return FLUID_ERR_INVALID_ARGUMENT; }
+    s->tick += 1;
+    s->make_uniform(*t, s->tick, &s->last_uniform);
+    s->slab_params = s->make_params(s->last_uniform);
+    s->n_marks = 0;
+    s->mark("begin");
+    const uint32_t max_tiles = (s->slab_capacity + 2u * s->slab_pad + SORT_TILE - 1) / SORT_TILE;
+    FLUID_CUDA(cudaMemsetAsync(s->sort_scratch, 0, ((size_t)MAX_PASSES * RADIX + RADIX + (size_t)s->sort_passes * max_tiles * RADIX) * 4, s->stream));
+    FLUID_CUDA(cudaMemsetAsync(s->emig_list, 0xff, (size_t)s->emig_cap * 8, s->stream));
+    FLUID_CUDA(cudaMemsetAsync(s->emig_count, 0, 4, s->stream));
+    slab_hash(s, s->slab_params, s->state_off, s->n, 1, s->d_frame_time);
+    s->mark("predict+key+hist");
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+
+// phases 3+4: keys of the immigrants, sort of [from below | natives | from above], gather into key order,
+// band metadata. Afterwards the handle owns n_total - n_emigrants particles.
+int fluid_slab_sort(FluidSim* h, uint32_t n_from_below, uint32_t n_from_above, uint32_t n_emigrants) {
+    SLAB_OR_FAIL(h);
+    if (n_from_below > s->slab_pad || n_from_above > s->slab_pad) { set_error("fluid_slab_sort: more immigrants than the pad holds"); return FLUID_ERR_INVALID_ARGUMENT; }
+    const uint32_t begin = s->state_off - n_from_below;
+    const uint32_t total = n_from_below + s->n + n_from_above;
+    if (n_emigrants > s->n || total - n_emigrants > s->slab_capacity) { set_error("fluid_slab_sort: band overflows its capacity"); return FLUID_ERR_INVALID_ARGUMENT; }
+    DevParams& p = s->slab_params;
+    slab_hash(s, p, begin, n_from_below, 0, nullptr);
+    slab_hash(s, p, s->state_off + s->n, n_from_above, 0, nullptr);
+    const uint32_t passes = s->sort_passes;
+    uint32_t* hist = s->sort_scratch;
+    uint32_t* counters = s->sort_scratch + MAX_PASSES * RADIX;
+    uint32_t* status = counters + RADIX;
+    k_scan_histograms<<<passes, RADIX, 0, s->stream>>>(hist);
+    s->launches++;
+    const uint32_t tiles = (total + SORT_TILE - 1) / SORT_TILE;
+    const size_t sort_smem = (size_t)SORT_TILE * 2 * sizeof(uint32_t);
+    const uint32_t* kin = s->keys_u + begin;
+    const uint32_t* vin = nullptr;
+    uint32_t* kout = s->keys_b;
+    uint32_t* vout = s->idx_a;
+    for (uint32_t q = 0; q < passes && tiles > 0; q++) {
+        if (q == 0)
+            k_onesweep_pass<SORT_ITEMS, true><<<tiles, SORT_THREADS, sort_smem, s->stream>>>(
+                kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, total, (int)(q * RADIX_BITS));
+        else
+            k_onesweep_pass<SORT_ITEMS, false><<<tiles, SORT_THREADS, sort_smem, s->stream>>>(
+                kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, total, (int)(q * RADIX_BITS));
+        s->launches++;
+        kin = kout; vin = vout;
+        kout = (kout == s->keys_b) ? s->keys_c : s->keys_b;
+        vout = (vout == s->idx_a) ? s->idx_b : s->idx_a;
+    }
+    s->keys_sorted = const_cast<uint32_t*>(kin);
+    s->idx_sorted = const_cast<uint32_t*>(vin);
+    s->mark("sort");
+    s->n = total - n_emigrants;  // sentinel keys sorted to the tail and are dropped here
+    p.n = s->n;
+    p.own_begin = s->sorted_off;
+    if (s->n) {
+        k_slab_gather<<<(s->n + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
+            p, s->keys_sorted, s->idx_sorted, s->pos_a + begin, s->vel_a + begin, s->pos_s, s->pred_s, s->vel_s, s->keys_ext);
+        s->launches++;
+    }
+    const uint32_t row_first = s->slab_rows.bounds[s->slab_rows.rank], row_end = s->slab_rows.bounds[s->slab_rows.rank + 1];
+    k_slab_meta<<<1, 32, 0, s->stream>>>(s->keys_ext + s->sorted_off, s->n, s->grid_w, row_first, row_end > row_first ? row_end - 1 : row_first,
+                                         s->start_indices, s->num_cells, s->slab_meta);
+    s->launches++;
+    s->mark("gather");
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+
+// phases 6+7a: halo keys, cell tables over [halo | owned | halo], density of the owned particles
+int fluid_slab_cells_density(FluidSim* h, uint32_t halo_below, uint32_t halo_above, uint32_t global_offset, uint32_t quirk_c0,
+                             uint32_t quirk_stale_ext) {
+    SLAB_OR_FAIL(h);
+    if (halo_below > s->slab_pad || halo_above > s->slab_pad) { set_error("fluid_slab_cells_density: halo larger than the pad"); return FLUID_ERR_INVALID_ARGUMENT; }
+    DevParams& p = s->slab_params;
+    p.ext_begin = s->sorted_off - halo_below;
+    p.ext_end = s->sorted_off + s->n + halo_above;
+    p.global_offset = global_offset;
+    const uint32_t halos = halo_below + halo_above;
+    if (halos) {
+        k_slab_halo_keys<<<(halos + 255) / 256, 256, 0, s->stream>>>(p, s->pred_s, s->keys_ext, p.ext_begin, halo_below,
+                                                                     s->sorted_off + s->n, halo_above);
+        s->launches++;
+    }
+    const uint32_t ext = p.ext_end - p.ext_begin;
+    if (ext) {
+        k_slab_build_cells<<<(ext + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
+            p, s->keys_ext, s->start_indices, s->cell_lb, s->quirk, quirk_c0, quirk_stale_ext);
+    } else {
+        k_slab_fill_table<<<(s->num_cells + 1 + 255) / 256, 256, 0, s->stream>>>(s->cell_lb, s->num_cells + 1, p.ext_begin);
+    }
+    s->launches++;
+    s->mark("cells");
+    if (s->n) {
+        k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho);
+        s->launches++;
+    }
+    s->mark("density");
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+
+// phase 7b: force + integrate over the owned particles; the new state lands at state_off in key order
+int fluid_slab_force(FluidSim* h) {
+    SLAB_OR_FAIL(h);
+    if (s->n) launch_force(s, s->slab_params, (s->n + SPH_THREADS - 1) / SPH_THREADS, s->pos_a + s->state_off, s->vel_a + s->state_off);
+    s->mark("force+integrate");
+    if (s->timing) { s->marks_per_tick = s->n_marks; s->timed_ticks++; }
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+
+}  // extern "C"

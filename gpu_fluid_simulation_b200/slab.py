@@ -1,0 +1,360 @@
+"""Slab (multi-GPU) mode: the domain is cut into bands of grid rows, one band per rank.
+
+One process per GPU; the device passes are libfluid_b200's fluid_slab_* phases (csrc/slab.inl); the three exchanges
+per tick move through torch.distributed (NCCL over NVLink) on zero-copy views of the handle's device arrays:
+
+  1. migration   particles whose predicted position left the band -> their new owner (all_to_all: counts, payload).
+                 Immigrants from lower ranks are placed before the natives, from higher ranks after them, in source
+                 order, so the stable sort reproduces the single-GPU tie order exactly.
+  2. halo        first / last grid row of (pred, vel) -> lower / upper neighbour (P2P send/recv)
+  3. halo rho    density of the same rows, after the density pass
+
+Keys stay global, so the concatenation of the ranks' sorted arrays IS the single-GPU sorted array, and every rank
+computes its particles with the neighbours in the same order as one GPU would: results are bit-identical to a
+single-GPU tick (tests/test_gpu_slab.py).
+
+`SlabRank` holds the per-rank phases and is transport-agnostic; `LocalDriver` runs several ranks in one process on
+one device (tests, no NCCL), `DistDriver` runs one rank per process over torch.distributed.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from .simulation import FluidSimulation, SimulationSettings, TickSettings
+
+NO_QUIRK = 0xFFFFFFFF
+
+
+def row_bounds(grid_h: int, world: int):
+    """bands of grid rows: rows 1..grid_h-2 can hold particles; the empty border rows go to the edge ranks."""
+    inner = max(grid_h - 2, 1)
+    per = -(-inner // world)
+    b = [0]
+    for r in range(1, world):
+        b.append(min(1 + r * per, grid_h))
+    b.append(grid_h)
+    return b
+
+
+class _DeviceArray:
+    """__cuda_array_interface__ wrapper so torch can view library-owned device memory without a copy."""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 3,
+                                         "strides": None}
+
+
+def _view(ptr, shape, typestr, device):
+    return torch.as_tensor(_DeviceArray(ptr, shape, typestr), device=device)
+
+
+class SlabRank:
+    """one rank's band. All methods only enqueue work on the handle's stream unless they say they synchronise."""
+
+    def __init__(self, device, settings: SimulationSettings, rank: int, world: int, capacity: int, pad: int,
+                 emig_cap: int = 1 << 16, math_mode: int = 0):
+        self.rank, self.world = rank, world
+        self.settings = settings
+        self.sim = FluidSimulation.new(device, SimulationSettings(particle_count=2, particle_spacing=settings.particle_spacing,
+                                                                  smoothing_radius=settings.smoothing_radius, size=settings.size,
+                                                                  texture_size=settings.texture_size))
+        self.sim.math_mode = math_mode
+        self.lib = self.sim._lib
+        self.h = self.sim._h
+        self.grid_w, self.grid_h = self.sim.grid_w, self.sim.grid_h
+        self.bounds = row_bounds(self.grid_h, world)
+        rb = (C.c_uint32 * (world + 1))(*self.bounds)
+        _lib.check(self.lib.fluid_slab_configure(self.h, rank, world, rb, int(capacity), int(pad), int(emig_cap)))
+        v = _lib.SlabView()
+        _lib.check(self.lib.fluid_slab_view(self.h, C.byref(v)))
+        self.pad, self.capacity, self.emig_cap = v.pad, v.capacity, v.emig_cap
+        self.device = torch.device("cuda", device)
+        total = self.capacity + 2 * self.pad
+        dv = self.device
+        self.pos_state = _view(v.pos_state, (total, 2), "<f4", dv)
+        self.vel_state = _view(v.vel_state, (total, 2), "<f4", dv)
+        self.pred_sorted = _view(v.pred_sorted, (total, 2), "<f4", dv)
+        self.vel_sorted = _view(v.vel_sorted, (total, 2), "<f4", dv)
+        self.rho = _view(v.rho, (total,), "<f4", dv)
+        self.emig_list = _view(v.emig_list, (self.emig_cap,), "<i8", dv)
+        self.meta = _view(v.meta, (16,), "<i4", dv)  # words 0..3 band metadata, word 8 emigrant counter
+        self.stream = torch.cuda.ExternalStream(self.sim.stream, device=dv)
+        self.n = 0
+        self.n_emig = 0
+        self.n_below = self.n_above = 0
+        self.halo_below = self.halo_above = 0
+
+    # ---- setup -------------------------------------------------------------------------------------------
+    def owns_rows(self):
+        return self.bounds[self.rank], self.bounds[self.rank + 1]
+
+    def upload_band(self, particles: np.ndarray):
+        """particles of this band in global array order (AoS)."""
+        self.n = int(particles.shape[0])
+        _lib.check(self.lib.fluid_sim_set_particle_count(self.h, self.n))
+        if self.n:
+            self.sim.upload_particles(np.ascontiguousarray(particles))
+        self.sim.sync()
+
+    def download_band(self) -> np.ndarray:
+        out = np.empty(self.n, dtype=_lib.PARTICLE_DTYPE)
+        if self.n:
+            _lib.check(self.lib.fluid_sim_download_particles(self.h, _lib.ptr(out)))
+        return out
+
+    # ---- phase 1: keys of the natives, emigrant list --------------------------------------------------------
+    def begin_tick(self, ts: TickSettings):
+        c = ts.to_c()
+        _lib.check(self.lib.fluid_slab_begin_tick(self.h, C.byref(c)))
+
+    def send_counts(self) -> torch.Tensor:
+        """int64[world] on the device: emigrants per destination rank (no host sync)."""
+        with torch.cuda.stream(self.stream):
+            # entries are (dest << 32 | index): ascending order = grouped by destination, source order inside a group
+            self._sorted_list = torch.sort(self.emig_list).values
+            valid = self._sorted_list >= 0  # unused slots hold 0xff.. = -1
+            dest = torch.where(valid, self._sorted_list >> 32, torch.full_like(self._sorted_list, self.world))
+            return torch.bincount(dest, minlength=self.world + 1)[: self.world].contiguous()
+
+    def pack(self, send_counts_host):
+        """payload float32[m, 4] = (pos, vel) of the emigrants grouped by destination, source order inside a group."""
+        m = int(sum(send_counts_host))
+        self.n_emig = m
+        if m > self.emig_cap:
+            raise _lib.FluidError(f"rank {self.rank}: {m} emigrants exceed emig_cap {self.emig_cap}")
+        with torch.cuda.stream(self.stream):
+            if m == 0:
+                return torch.empty((0, 4), dtype=torch.float32, device=self.device)
+            # unused slots (0xff.. = -1 as int64) sort first: the m valid entries are the LAST m of the ascending list
+            lst = self._sorted_list[self.emig_cap - m:]
+            idx = lst & 0xFFFFFFFF
+            return torch.cat([self.pos_state[idx], self.vel_state[idx]], dim=1).contiguous()
+
+    # ---- phase 2: immigrants in -------------------------------------------------------------------------------
+    def unpack(self, recv: torch.Tensor, recv_counts_host):
+        """recv float32[k, 4] ordered by source rank."""
+        nb = int(sum(recv_counts_host[: self.rank]))
+        na = int(sum(recv_counts_host[self.rank + 1:]))
+        if nb > self.pad or na > self.pad:
+            raise _lib.FluidError(f"rank {self.rank}: {nb}+{na} immigrants exceed the pad {self.pad}")
+        self.n_below, self.n_above = nb, na
+        P, n = self.pad, self.n
+        with torch.cuda.stream(self.stream):
+            if nb:
+                self.pos_state[P - nb:P] = recv[:nb, 0:2]
+                self.vel_state[P - nb:P] = recv[:nb, 2:4]
+            if na:
+                self.pos_state[P + n:P + n + na] = recv[nb:nb + na, 0:2]
+                self.vel_state[P + n:P + n + na] = recv[nb:nb + na, 2:4]
+
+    # ---- phases 3+4: sort, gather, metadata ---------------------------------------------------------------------
+    def sort(self):
+        _lib.check(self.lib.fluid_slab_sort(self.h, self.n_below, self.n_above, self.n_emig))
+        self.n = self.n + self.n_below + self.n_above - self.n_emig
+
+    def meta_tensor(self) -> torch.Tensor:
+        """int64[5] on the device: n_owned, first-row count, last-row count, key of first owned, its table entry."""
+        with torch.cuda.stream(self.stream):
+            m = self.meta[:4].to(torch.int64) & 0xFFFFFFFF
+            return torch.cat([torch.tensor([self.n], dtype=torch.int64, device=self.device), m])
+
+    # ---- phase 5: halo rows ------------------------------------------------------------------------------------------
+    def halo_out(self, first_count, last_count):
+        """(to_below, to_above): lists of contiguous views [pred, vel] of the band's first / last grid row."""
+        P, n = self.pad, self.n
+        self._first, self._last = int(first_count), int(last_count)
+        lo = slice(P, P + self._first)
+        hi = slice(P + n - self._last, P + n)
+        return [self.pred_sorted[lo], self.vel_sorted[lo]], [self.pred_sorted[hi], self.vel_sorted[hi]]
+
+    def halo_in(self, below_count, above_count):
+        P, n = self.pad, self.n
+        if below_count > self.pad or above_count > self.pad:
+            raise _lib.FluidError(f"rank {self.rank}: halo rows ({below_count}, {above_count}) exceed the pad {self.pad}")
+        self.halo_below, self.halo_above = int(below_count), int(above_count)
+        lo = slice(P - self.halo_below, P)
+        hi = slice(P + n, P + n + self.halo_above)
+        return [self.pred_sorted[lo], self.vel_sorted[lo]], [self.pred_sorted[hi], self.vel_sorted[hi]]
+
+    def rho_out(self):
+        P, n = self.pad, self.n
+        return self.rho[P:P + self._first], self.rho[P + n - self._last:P + n]
+
+    def rho_in(self):
+        P, n = self.pad, self.n
+        return self.rho[P - self.halo_below:P], self.rho[P + n:P + n + self.halo_above]
+
+    # ---- phases 6+7 ---------------------------------------------------------------------------------------------------
+    def cells_density(self, global_offset, quirk_c0, quirk_stale_global):
+        """quirk_*: lowest occupied cell of the whole domain and its stale start_indices entry (a GLOBAL sorted index)."""
+        if quirk_c0 == NO_QUIRK:
+            stale_ext = 0
+        else:
+            ext_begin = self.pad - self.halo_below
+            s = int(quirk_stale_global) - int(global_offset) + self.pad
+            stale_ext = min(max(s, ext_begin), 0xFFFFFFFF)
+        _lib.check(self.lib.fluid_slab_cells_density(self.h, self.halo_below, self.halo_above, int(global_offset),
+                                                     int(quirk_c0) & 0xFFFFFFFF, int(stale_ext)))
+
+    def force(self):
+        _lib.check(self.lib.fluid_slab_force(self.h))
+
+    def sync(self):
+        self.sim.sync()
+
+    def close(self):
+        self.sim.close()
+
+
+def _quirk_from_metas(metas):
+    """metas: int array [world, 5]. The lowest occupied cell belongs to the first non-empty rank."""
+    for r in range(metas.shape[0]):
+        if metas[r, 0] > 0:
+            return int(metas[r, 3]), int(metas[r, 4])
+    return NO_QUIRK, 0
+
+
+class LocalDriver:
+    """several SlabRanks in ONE process on one device, exchanging through device copies (tests; no NCCL).
+    Ranks run one after another, so nothing ever waits on another rank's kernel."""
+
+    def __init__(self, ranks):
+        self.ranks = ranks
+        self.world = len(ranks)
+
+    def _sync(self):
+        for r in self.ranks:
+            r.sync()
+        torch.cuda.synchronize()
+
+    def tick(self, ts: TickSettings):
+        R, W = self.ranks, self.world
+        for r in R:
+            r.begin_tick(ts)
+        counts = torch.stack([r.send_counts() for r in R]).cpu().numpy()  # [src, dst]; synchronises
+        payloads = [r.pack(counts[i]) for i, r in enumerate(R)]
+        self._sync()
+        for d, r in enumerate(R):
+            parts = []
+            for s_ in range(W):
+                off = int(counts[s_, :d].sum())
+                parts.append(payloads[s_][off:off + int(counts[s_, d])])
+            r.unpack(torch.cat(parts) if parts else payloads[0][:0], counts[:, d])
+        self._sync()
+        for r in R:
+            r.sort()
+        metas = torch.stack([r.meta_tensor() for r in R]).cpu().numpy()
+        prefix = np.concatenate([[0], np.cumsum(metas[:, 0])])
+        c0, stale = _quirk_from_metas(metas)
+        outs = [r.halo_out(metas[i, 1], metas[i, 2]) for i, r in enumerate(R)]
+        ins = [r.halo_in(metas[i - 1, 2] if i > 0 else 0, metas[i + 1, 1] if i + 1 < W else 0) for i, r in enumerate(R)]
+        self._sync()
+        for i in range(W):
+            if i > 0:
+                for dst, src in zip(ins[i][0], outs[i - 1][1]):
+                    dst.copy_(src)
+            if i + 1 < W:
+                for dst, src in zip(ins[i][1], outs[i + 1][0]):
+                    dst.copy_(src)
+        self._sync()
+        for i, r in enumerate(R):
+            r.cells_density(int(prefix[i]), c0, stale)
+        self._sync()
+        rho_o = [r.rho_out() for r in R]
+        rho_i = [r.rho_in() for r in R]
+        for i in range(W):
+            if i > 0:
+                rho_i[i][0].copy_(rho_o[i - 1][1])
+            if i + 1 < W:
+                rho_i[i][1].copy_(rho_o[i + 1][0])
+        self._sync()
+        for r in R:
+            r.force()
+        self._sync()
+        self.last_metas = metas
+
+
+class DistDriver:
+    """one SlabRank per process; exchanges over torch.distributed (NCCL on GPUs, gloo in CPU tests of the protocol)."""
+
+    def __init__(self, rank_obj, group=None):
+        import torch.distributed as dist
+        self.dist = dist
+        self.r = rank_obj
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.exchange_bytes = 0
+
+    def tick(self, ts: TickSettings):
+        dist, r, W, me = self.dist, self.r, self.world, self.rank
+        with torch.cuda.stream(r.stream):
+            r.begin_tick(ts)
+            # ---- migration: counts, then payload ----
+            sc = r.send_counts()
+            rc = torch.empty_like(sc)
+            dist.all_to_all_single(rc, sc, group=self.group)
+            both = torch.stack([sc, rc]).cpu().numpy()  # synchronises
+            send_counts, recv_counts = both[0], both[1]
+            payload = r.pack(send_counts)
+            recv = torch.empty((int(recv_counts.sum()), 4), dtype=torch.float32, device=r.device)
+            if int(send_counts.sum()) or int(recv_counts.sum()) or True:
+                dist.all_to_all_single(recv, payload, output_split_sizes=[int(x) for x in recv_counts],
+                                       input_split_sizes=[int(x) for x in send_counts], group=self.group)
+            r.unpack(recv, recv_counts)
+            r.sort()
+            # ---- band metadata of every rank ----
+            m = r.meta_tensor()
+            allm = torch.empty((W, m.numel()), dtype=m.dtype, device=r.device)
+            dist.all_gather_into_tensor(allm, m, group=self.group)
+            metas = allm.cpu().numpy()  # synchronises
+            prefix = np.concatenate([[0], np.cumsum(metas[:, 0])])
+            c0, stale = _quirk_from_metas(metas)
+            # ---- halo rows of (pred, vel) ----
+            to_below, to_above = r.halo_out(metas[me, 1], metas[me, 2])
+            from_below, from_above = r.halo_in(metas[me - 1, 2] if me > 0 else 0, metas[me + 1, 1] if me + 1 < W else 0)
+            ops = []
+            for k in range(2):
+                if me > 0 and to_below[k].shape[0]:
+                    ops.append(dist.P2POp(dist.isend, to_below[k], me - 1, group=self.group))
+                if me + 1 < W and to_above[k].shape[0]:
+                    ops.append(dist.P2POp(dist.isend, to_above[k], me + 1, group=self.group))
+                if me > 0 and from_below[k].shape[0]:
+                    ops.append(dist.P2POp(dist.irecv, from_below[k], me - 1, group=self.group))
+                if me + 1 < W and from_above[k].shape[0]:
+                    ops.append(dist.P2POp(dist.irecv, from_above[k], me + 1, group=self.group))
+            if ops:
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
+            r.cells_density(int(prefix[me]), c0, stale)
+            # ---- halo rho ----
+            ro_b, ro_a = r.rho_out()
+            ri_b, ri_a = r.rho_in()
+            ops = []
+            if me > 0 and ro_b.shape[0]:
+                ops.append(dist.P2POp(dist.isend, ro_b, me - 1, group=self.group))
+            if me + 1 < W and ro_a.shape[0]:
+                ops.append(dist.P2POp(dist.isend, ro_a, me + 1, group=self.group))
+            if me > 0 and ri_b.shape[0]:
+                ops.append(dist.P2POp(dist.irecv, ri_b, me - 1, group=self.group))
+            if me + 1 < W and ri_a.shape[0]:
+                ops.append(dist.P2POp(dist.irecv, ri_a, me + 1, group=self.group))
+            if ops:
+                for w in dist.batch_isend_irecv(ops):
+                    w.wait()
+            r.force()
+        self.last_metas = metas
+        self.exchange_bytes = int(16 * (send_counts.sum() + recv_counts.sum()) + 20 * (r.halo_below + r.halo_above + r._first + r._last))
+
+
+def split_particles(particles: np.ndarray, settings: SimulationSettings, bounds):
+    """initial distribution: by the grid row of the CURRENT predicted position's key, preserving array order.
+    (Ownership is re-derived from the keys of each tick, so any consistent initial split works; this one makes the
+    first tick migration-free for particles at rest.)"""
+    h = np.float32(settings.smoothing_radius)
+    half = np.float32(settings.size[1]) * np.float32(0.5)
+    row = np.floor((particles["predicted_position"][:, 1] + half) / h).astype(np.int64) + 1
+    owner = np.searchsorted(np.asarray(bounds[1:-1]), row, side="right")
+    return [particles[owner == r] for r in range(len(bounds) - 1)]

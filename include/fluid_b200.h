@@ -203,12 +203,45 @@ int fluid_sim_last_timing(FluidSim* sim, const char** names, float* ms, int cap)
 /* number of kernels this library has launched on the handle since creation. */
 uint64_t fluid_sim_launch_count(const FluidSim* sim);
 
-/* ---- slab (multi-GPU) support: the handle may own a y-slab of the domain ------- */
-
-/* Replace the particle set (count may change, <= capacity given at creation via
- * fluid_sim_reserve). Used by migration / halo refresh. */
+/* ---- capacity / particle count ----------------------------------------------------- */
 int fluid_sim_reserve(FluidSim* sim, uint32_t capacity);
 int fluid_sim_set_particle_count(FluidSim* sim, uint32_t n);
+
+/* ---- slab (multi-GPU) mode: SURVEY.md §8(e) -------------------------------------------
+ * One handle per rank owns a band of grid rows [row_bounds[rank], row_bounds[rank+1]). Keys stay global. The host
+ * drives the phases below and performs the three exchanges between them (migration, halo pred+vel, halo rho) with
+ * NCCL on views of the handle's device arrays (FluidSlabView); see gpu_fluid_simulation_b200/slab.py. The reference
+ * has no multi-GPU code; the contract is that the gathered result equals a single-GPU tick of the same state. */
+typedef struct FluidSlabView {
+    uint32_t n;            /* particles currently owned */
+    uint32_t pad;          /* state arrays: natives start at index pad; key-ordered arrays: owned start at pad */
+    uint32_t capacity;
+    uint32_t emig_cap;
+    void* pos_state;       /* float2[pad + capacity + pad] */
+    void* vel_state;
+    void* pos_sorted;      /* float2[...] key order, [halo below | owned | halo above] around index pad */
+    void* pred_sorted;
+    void* vel_sorted;
+    void* rho;             /* float[...] */
+    void* keys_ext;        /* uint32[...] */
+    void* emig_list;       /* uint64[emig_cap]: (destination rank << 32) | index into the state arrays; 0xff.. = unused */
+    void* emig_count;      /* uint32 */
+    void* meta;            /* uint32[4]: first-row count, last-row count, key of first owned, its start_indices entry */
+    void* start_indices;   /* uint32[grid_w*grid_h], global sorted indices for the cells this rank owns */
+} FluidSlabView;
+int fluid_slab_configure(FluidSim* sim, int rank, int world, const uint32_t* row_bounds /* world+1 */, uint32_t capacity,
+                         uint32_t pad, uint32_t emig_cap);
+int fluid_slab_view(FluidSim* sim, FluidSlabView* out);
+/* phase 1: tick += 1; keys of the natives; emigrants listed and given the sentinel key */
+int fluid_slab_begin_tick(FluidSim* sim, const FluidTickSettings* tick);
+/* phase 3+4: keys of the immigrants (already copied in around the natives), sort, gather, band metadata */
+int fluid_slab_sort(FluidSim* sim, uint32_t n_from_below, uint32_t n_from_above, uint32_t n_emigrants);
+/* phase 6+7a: halo keys, cell tables, density. quirk_*: lowest occupied cell of the whole domain and its stale
+ * start_indices entry translated to this rank's key-ordered index space (0xffffffff, 0 when not visible) */
+int fluid_slab_cells_density(FluidSim* sim, uint32_t halo_below, uint32_t halo_above, uint32_t global_offset,
+                             uint32_t quirk_c0, uint32_t quirk_stale_ext);
+/* phase 7b: force + integrate of the owned particles */
+int fluid_slab_force(FluidSim* sim);
 
 /* ---- jump-flood distance field (reference: shaders/jump_flood.wgsl:17-65; the host
  *      protocol is pinned in SURVEY.md §8 row a7) ---------------------------------- */
