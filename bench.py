@@ -181,7 +181,7 @@ def main():
     torch.cuda.set_device(local_rank)
     if world > 1:
         from gpu_fluid_simulation_b200.slab import run_slab_bench
-        line = run_slab_bench(args, rank, world, local_rank)
+        line = run_slab_bench(args, rank, world, local_rank, WORKLOADS, ALGO_BYTES, *peaks(), ClockSampler)
         if rank == 0:
             print(json.dumps(line), flush=True)
         return
@@ -237,7 +237,7 @@ def main():
     if os.path.exists(traffic_path):
         with open(traffic_path) as f:
             tj = json.load(f)
-        roofline["traffic"] = tj.get(args.workload, {}).get(roofline["kernel"])
+        roofline["traffic"] = tj.get(args.workload, {}).get(roofline["kernel"])  # bytes per launch, ncu (profiles/)
 
     # ---- end to end through the public API with host buffers -------------------------------------
     e2e = None

@@ -13,10 +13,11 @@ SEED_VEL = 0xF1D00002
 _M = (1 << 64) - 1
 
 
-def splitmix64(seed: int, count: int) -> np.ndarray:
-    """`count` uniform doubles in [0,1) from splitmix64 (vectorised: state_i = seed + (i+1)*golden)."""
+def splitmix64(seed: int, count: int, start: int = 0) -> np.ndarray:
+    """draws start .. start+count-1 of the splitmix64 stream as doubles in [0,1) (state_i = seed + (i+1)*golden, so any
+    sub-range can be generated on its own: each rank of a slab run builds only its band)."""
     with np.errstate(over="ignore"):
-        i = np.arange(1, count + 1, dtype=np.uint64)
+        i = np.arange(start + 1, start + count + 1, dtype=np.uint64)
         z = np.uint64(seed & _M) + i * np.uint64(0x9E3779B97F4A7C15)
         z = (z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
         z = (z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
@@ -24,30 +25,35 @@ def splitmix64(seed: int, count: int) -> np.ndarray:
     return (z >> np.uint64(11)).astype(np.float64) * (1.0 / (1 << 53))
 
 
-def _block(cols: int, rows: int, spacing: float, x0: float, y0: float, jitter: float, vel_amp: float):
-    n = cols * rows
-    ix = (np.arange(n, dtype=np.int64) % cols).astype(np.float64)
-    iy = (np.arange(n, dtype=np.int64) // cols).astype(np.float64)
-    r = splitmix64(SEED_JITTER, 2 * n)
+def _block(cols: int, rows: int, spacing: float, x0: float, y0: float, jitter: float, vel_amp: float, i0: int = 0, i1=None):
+    """particles i0 .. i1-1 of the cols x rows jittered lattice (row-major)."""
+    i1 = cols * rows if i1 is None else i1
+    n = i1 - i0
+    idx = np.arange(i0, i1, dtype=np.int64)
+    ix = (idx % cols).astype(np.float64)
+    iy = (idx // cols).astype(np.float64)
+    r = splitmix64(SEED_JITTER, 2 * n, 2 * i0)
     px = x0 + (ix + 0.5) * spacing + (r[0::2] * 2.0 - 1.0) * jitter * spacing
     py = y0 + (iy + 0.5) * spacing + (r[1::2] * 2.0 - 1.0) * jitter * spacing
     p = np.zeros(n, dtype=PARTICLE_DTYPE)
     p["position"][:, 0] = px.astype(np.float32)
     p["position"][:, 1] = py.astype(np.float32)
     if vel_amp != 0.0:
-        v = splitmix64(SEED_VEL, 2 * n)
+        v = splitmix64(SEED_VEL, 2 * n, 2 * i0)
         p["velocity"][:, 0] = ((v[0::2] * 2.0 - 1.0) * vel_amp).astype(np.float32)
         p["velocity"][:, 1] = ((v[1::2] * 2.0 - 1.0) * vel_amp).astype(np.float32)
     p["predicted_position"] = p["position"]
     return p
 
 
-def uniform_box(n_side: int, spacing=0.1, h=0.2, tex=(1024, 1024)):
-    """Scene U: n x n jittered lattice filling size = (n*s, n*s); vel uniform in [-1,1]^2."""
+def uniform_box(n_side: int, spacing=0.1, h=0.2, tex=(1024, 1024), lattice_rows=None):
+    """Scene U: n x n jittered lattice filling size = (n*s, n*s); vel uniform in [-1,1]^2.
+    lattice_rows=(r0, r1) returns only the particles of lattice rows r0..r1-1 (a contiguous range of the full array)."""
     size = (n_side * spacing, n_side * spacing)
     settings = SimulationSettings(particle_count=n_side * n_side, particle_spacing=spacing, smoothing_radius=h,
                                   size=size, texture_size=tex)
-    p = _block(n_side, n_side, spacing, -size[0] / 2, -size[1] / 2, 0.25, 1.0)
+    r0, r1 = (0, n_side) if lattice_rows is None else lattice_rows
+    p = _block(n_side, n_side, spacing, -size[0] / 2, -size[1] / 2, 0.25, 1.0, r0 * n_side, r1 * n_side)
     return settings, TickSettings(), p
 
 

@@ -358,3 +358,121 @@ def split_particles(particles: np.ndarray, settings: SimulationSettings, bounds)
     row = np.floor((particles["predicted_position"][:, 1] + half) / h).astype(np.int64) + 1
     owner = np.searchsorted(np.asarray(bounds[1:-1]), row, side="right")
     return [particles[owner == r] for r in range(len(bounds) - 1)]
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# bench.py --gpus N (N > 1): the uniform-box workload partitioned into y-slabs, one rank per GPU, NCCL exchanges
+# ------------------------------------------------------------------------------------------------------------------
+def band_of_uniform_box(n_side, rank, world, spacing=0.1, h=0.2):
+    """this rank's particles of the uniform-box scene, generated locally (no rank ever holds the whole scene).
+    Lattice rows 2k, 2k+1 (spacing = h/2, jitter < spacing/2) lie in grid row k+1."""
+    from . import scenes
+    settings, ts, _ = scenes.uniform_box(n_side, spacing, h, lattice_rows=(0, 0))
+    gh = int(np.ceil(np.float32(settings.size[1]) / np.float32(h))) + 2
+    b = row_bounds(gh, world)
+    lo, hi = max(b[rank], 1), b[rank + 1]
+    r0, r1 = min(2 * (lo - 1), n_side), min(2 * (hi - 1), n_side)
+    _, _, p = scenes.uniform_box(n_side, spacing, h, lattice_rows=(r0, max(r0, r1)))
+    return settings, ts, p
+
+
+def run_slab_bench(args, rank, world, local_rank, workloads, algo_bytes, peak, peak_src, sampler_cls):
+    import time
+    import torch.distributed as dist
+    kind, arg = workloads[args.workload]
+    if kind != "uniform":
+        raise SystemExit("--gpus > 1 benches the uniform-box workloads (BASELINE.json config 5)")
+    if not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    settings, ts, band = band_of_uniform_box(arg, rank, world)
+    n_total = settings.particle_count
+    per_row = 4 * (int(np.ceil(settings.size[0] / settings.smoothing_radius)) + 2)  # ~4 particles per cell
+    pad = max(4 * per_row, 1 << 14)
+    cap = int(band.shape[0] * 1.1) + 8 * per_row
+    r = SlabRank(local_rank, settings, rank, world, capacity=cap, pad=pad, emig_cap=max(1 << 16, 8 * per_row),
+                 math_mode=1 if args.math == "fast" else 0)
+    r.upload_band(band)
+    del band
+    drv = DistDriver(r)
+    for _ in range(args.warmup):
+        drv.tick(ts)
+    r.sync()
+    dist.barrier()
+    torch.cuda.synchronize()
+    sampler = sampler_cls(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = r.sim.launch_count
+    r.sim.enable_timing(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(r.stream)
+    for _ in range(args.steps):
+        drv.tick(ts)
+    e1.record(r.stream)
+    r.sync()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=r.device)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms = float(ms.item())
+    clocks = sampler.stop() if rank == 0 else None
+    phases = r.sim.last_timing()
+    r.sim.enable_timing(False)
+    launches = torch.tensor([r.sim.launch_count - launches0], dtype=torch.int64, device=r.device)
+    owned = torch.tensor([r.n], dtype=torch.int64, device=r.device)
+    dist.all_reduce(launches)
+    all_owned = [torch.zeros_like(owned) for _ in range(world)]
+    dist.all_gather(all_owned, owned)
+    assert int(sum(int(x.item()) for x in all_owned)) == n_total, "particles were lost or duplicated in migration"
+    exch = torch.tensor([drv.exchange_bytes], dtype=torch.int64, device=r.device)
+    dist.all_reduce(exch)
+
+    # ---- end to end: every rank uploads its band from pinned host memory, ticks, downloads it ----
+    e2e = None
+    if not args.no_e2e:
+        k = max(1, args.e2e_steps)
+        host = torch.empty((r.capacity, 8), dtype=torch.float32).pin_memory()
+        view = host.numpy().view(_lib.PARTICLE_DTYPE).reshape(-1)
+        h2d = d2h = 0
+        dist.barrier()
+        t0 = time.perf_counter()
+        for _ in range(k):
+            n_now = r.n
+            _lib.check(r.lib.fluid_sim_download_particles(r.h, _lib.ptr(host)))  # synchronises
+            d2h += n_now * 32
+            _lib.check(r.lib.fluid_sim_upload_particles(r.h, _lib.ptr(host)))
+            h2d += n_now * 32
+            drv.tick(ts)
+        r.sync()
+        dist.barrier()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=r.device)
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        tot = torch.tensor([h2d, d2h], dtype=torch.int64, device=r.device)
+        dist.all_reduce(tot)
+        e2e = {"value": n_total * k / float(dt.item()), "unit": "particle-steps/s", "h2d_bytes_per_step": int(tot[0].item()) // k,
+               "d2h_bytes_per_step": int(tot[1].item()) // k, "steps": k, "ms_per_step": 1e3 * float(dt.item()) / k,
+               "note": "every rank: download band to pinned host AoS + upload it back + tick (all exchanges), per step"}
+        del host, view
+
+    ms_per_step = ms / args.steps
+    ph = dict(phases)
+    dom_ms = ph.get("force+integrate", 0.0)
+    n_rank = int(all_owned[rank].item())
+    achieved = algo_bytes["force+integrate"] * n_rank / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    line = {"metric": "particle-steps/sec", "value": n_total * args.steps / (ms * 1e-3), "unit": "particle-steps/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload, "particles": n_total, "math": args.math,
+                       "parallelism": f"{world} y-slabs of grid rows, one rank per GPU; NCCL all_to_all migration + P2P halo rows",
+                       "particles_per_rank": [int(x.item()) for x in all_owned],
+                       "l2": "inputs larger than L2 (no flush)" if n_total * 64 / world > 252e6 else "per-rank state fits L2; steps run back to back (no flush)",
+                       "exchange_bytes_per_step_all_ranks": int(exch.item())},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches.item()),
+            "roofline": {"bound": "hbm", "kernel": "k_force_integrate (rank 0)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_particle": algo_bytes["force+integrate"], "kernel_ms": dom_ms,
+                         "share_of_step": dom_ms / ms_per_step if ms_per_step else None,
+                         "phases_ms_rank0_incl_exchange_waits": {k_: round(v, 5) for k_, v in phases}},
+            "cpu_baseline": None}
+    r.close()
+    dist.barrier()
+    return line
