@@ -86,6 +86,10 @@ class SlabRank:
         self.n_below = self.n_above = 0
         self.halo_below = self.halo_above = 0
 
+    def stream_ctx(self):
+        """torch ops and NCCL calls issued inside are ordered on the handle's CUDA stream."""
+        return torch.cuda.stream(self.stream)
+
     # ---- setup -------------------------------------------------------------------------------------------
     def owns_rows(self):
         return self.bounds[self.rank], self.bounds[self.rank + 1]
@@ -290,7 +294,7 @@ class DistDriver:
 
     def tick(self, ts: TickSettings):
         dist, r, W, me = self.dist, self.r, self.world, self.rank
-        with torch.cuda.stream(r.stream):
+        with r.stream_ctx():
             r.begin_tick(ts)
             # ---- migration: counts, then payload ----
             sc = r.send_counts()
@@ -307,9 +311,9 @@ class DistDriver:
             r.sort()
             # ---- band metadata of every rank ----
             m = r.meta_tensor()
-            allm = torch.empty((W, m.numel()), dtype=m.dtype, device=r.device)
+            allm = torch.empty(W * m.numel(), dtype=m.dtype, device=r.device)
             dist.all_gather_into_tensor(allm, m, group=self.group)
-            metas = allm.cpu().numpy()  # synchronises
+            metas = allm.view(W, -1).cpu().numpy()  # synchronises
             prefix = np.concatenate([[0], np.cumsum(metas[:, 0])])
             c0, stale = _quirk_from_metas(metas)
             # ---- halo rows of (pred, vel) ----

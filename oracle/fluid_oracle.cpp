@@ -319,8 +319,11 @@ void oracle_calculate_density(const U* u, P* p, const uint32_t* start_indices, i
 }
 
 // compute.wgsl:160-235  calculate_pressure_force. abs_terms (optional) accumulates sum |term|.
-static V2 pressure_force(const U& u, const P* p, const uint32_t* start_indices, uint32_t pid, V2* abs_terms) {
-    uint32_t rand_seed = pid * 12u + u.frame_time * 69u;
+// index_offset: added to the particle's array index to form the id the shader seeds its RNG with. 0 for the
+// reference's single array; in the slab tests the array is [halo | band | halo] of a larger sorted array.
+static V2 pressure_force(const U& u, const P* p, const uint32_t* start_indices, uint32_t pid, V2* abs_terms,
+                         uint32_t index_offset = 0) {
+    uint32_t rand_seed = (pid + index_offset) * 12u + u.frame_time * 69u;
     const P& me = p[pid];
     float pressure = calculate_pressure(u, me.density);
     float px = me.predicted_position[0], py = me.predicted_position[1];
@@ -413,17 +416,30 @@ static V2 viscosity_force(const U& u, const P* p, const uint32_t* start_indices,
 // compute.wgsl:79-157  move_particle with JACOBI semantics [survey-pinned, SURVEY.md §3.3]:
 // every neighbour read sees the state as it was when the pass started (`in`), results go to `out`.
 // accel_out / abs_out (optional, 2 floats per particle): pressure+viscosity sum and sum of |terms|.
+static void move_particle_range(const U* up, const P* in, P* out, const uint32_t* start_indices, const float* texture,
+                                float* accel_out, float* abs_out, uint32_t begin, uint32_t end, uint32_t index_offset);
+
 void oracle_move_particle(const U* up, const P* in, P* out, const uint32_t* start_indices, const float* texture,
                           float* accel_out, float* abs_out) {
+    move_particle_range(up, in, out, start_indices, texture, accel_out, abs_out, 0, up->particle_count, 0);
+}
+// slab tests: move only particles [begin, end) of the array (the rest are halo copies owned by other ranks);
+// RNG ids are array index + index_offset (wrapping u32), i.e. the particle's index in the global sorted array.
+void oracle_move_particle_range(const U* up, const P* in, P* out, const uint32_t* start_indices, const float* texture,
+                                uint32_t begin, uint32_t end, uint32_t index_offset) {
+    move_particle_range(up, in, out, start_indices, texture, nullptr, nullptr, begin, end, index_offset);
+}
+
+static void move_particle_range(const U* up, const P* in, P* out, const uint32_t* start_indices, const float* texture,
+                                float* accel_out, float* abs_out, uint32_t begin, uint32_t end, uint32_t index_offset) {
     const U& u = *up;
-    const uint32_t n = u.particle_count;
     const uint64_t tex_len = (uint64_t)f2u(u.texture_size[0]) * f2u(u.texture_size[1]);
 #pragma omp parallel for schedule(dynamic, 1024)
-    for (int64_t ii = 0; ii < (int64_t)n; ii++) {
+    for (int64_t ii = (int64_t)begin; ii < (int64_t)end; ii++) {
         uint32_t id = (uint32_t)ii;
         P particle = in[id];
         V2 abs_terms = v2(0.0f, 0.0f);
-        V2 pr = pressure_force(u, in, start_indices, id, abs_out ? &abs_terms : nullptr);
+        V2 pr = pressure_force(u, in, start_indices, id, abs_out ? &abs_terms : nullptr, index_offset);
         V2 vi = viscosity_force(u, in, start_indices, id, abs_out ? &abs_terms : nullptr);
         float ax = pr.x + vi.x, ay = pr.y + vi.y;
         if (accel_out) { accel_out[2 * ii] = ax; accel_out[2 * ii + 1] = ay; }

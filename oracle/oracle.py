@@ -161,6 +161,14 @@ def move_particle(u, p_in, table, texture, want_debug=False):
     return (out, accel, absum) if want_debug else out
 
 
+def move_particle_range(u, p_in, table, texture, begin, end, index_offset):
+    """slab tests: move only [begin, end); RNG ids = array index + index_offset."""
+    out = p_in.copy()
+    lib().oracle_move_particle_range(C.byref(u), _p(p_in), _p(out), _p(table), _p(texture), C.c_uint32(begin), C.c_uint32(end),
+                                     C.c_uint32(index_offset & 0xFFFFFFFF))
+    return out
+
+
 SORT_STABLE, SORT_BITONIC, SORT_COUNTING = 0, 1, 2
 
 
