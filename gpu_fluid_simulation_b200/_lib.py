@@ -113,6 +113,8 @@ PROTOTYPES = {
     "fluid_jfa_seed_from_particles": (_i, [_P, _u32, C.POINTER(C.c_float * 2), _u32, _u32, _P, _i]),
     "fluid_jfa_to_force_field": (_i, [_P, _u32, _u32, _P, _i]),
     "fluid_sim_jfa_from_particles": (_i, [_P, _u32, _u32, _P, _P, _i, C.POINTER(C.c_float)]),
+    "fluid_selftest_division": (_i, [_i, _u32, _i, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
+                                     C.POINTER(C.c_float)]),
 }
 
 _lib = None

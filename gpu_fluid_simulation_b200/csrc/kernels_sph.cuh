@@ -264,31 +264,68 @@ struct ForceAcc {
 //   !EXACT ("fast"): one MUFU.RSQ gives 1/r (so r = sq/r', dir = d/r', h/(2r)) and one MUFU.RCP gives 1/rho_j;
 //   FMA contraction allowed; constants' reciprocals hoisted. Agrees with EXACT to a few ulp per term
 //   (tests bound it by 1e-5 of sum|terms|); branch decisions (r2 cut-off, r == 0, r <= h) are unchanged.
+// per-thread loop invariants of the exact pair body: refined reciprocals of the two constant denominators
+struct PairConsts {
+    float y_two_h3, y_h2;
+    bool fast_div;  // h2, two_h3 in the shared-reciprocal range (else every pair takes the __fdiv_rn body)
+};
+__device__ __forceinline__ PairConsts make_pair_consts(const DevParams& p) {
+    PairConsts c;
+    c.y_two_h3 = rcp_refined(p.two_h3);
+    c.y_h2 = rcp_refined(p.h2);
+    c.fast_div = p.two_h3 >= DIV_DEN_LO && p.two_h3 <= DIV_DEN_HI && p.h2 >= DIV_DEN_LO && p.h2 <= DIV_DEN_HI &&
+                 p.h >= DIV_DEN_LO && p.h <= DIV_DEN_HI;
+    return c;
+}
+
 template <bool DEBUG, bool EXACT>
-__device__ __forceinline__ void force_pair(const DevParams& p, float dx, float dy, float sq, float2 nv, float nd, float vx,
-                                           float vy, float pressure, uint32_t& rand_seed, ForceAcc& acc) {
+__device__ __forceinline__ void force_pair(const DevParams& p, const PairConsts& c, float dx, float dy, float sq, float2 nv,
+                                           float nd, float vx, float vy, float pressure, uint32_t& rand_seed, ForceAcc& acc) {
     float tx, ty, ux, uy;
     if (EXACT) {
+        // Every quotient below is the correctly rounded one (== the CPU restatement's `/`). The common case
+        // computes the 9 divisions of a pair from 2 refined reciprocals (1/r, 1/rho_j; common.cuh div_by) and
+        // the two hoisted constant ones; operands outside the range where that is provably exact (r < 2^-20
+        // including the coincident-particle RNG branch, tiny non-zero or huge numerators) take __fdiv_rn.
         const float dst = fsqrt(sq);
-        float dirx, diry;
-        if (dst == 0.0f) {  // compute.wgsl:211-212
-            const float rx = rand_f32(rand_seed);
-            const float ry = rand_f32(rand_seed);
-            const float len = fsqrt(fadd(fmul(rx, rx), fmul(ry, ry)));
-            dirx = fdiv(rx, len); diry = fdiv(ry, len);
-        } else {
-            dirx = fdiv(dx, dst); diry = fdiv(dy, dst);
-        }
         const float np = fmul(p.pressure_constant, fsub(nd, p.rest_density));
-        const float k = (dst <= p.h) ? fmul(-fsub(p.h, dst), p.spiky) : 0.0f;  // funcs.wgsl:101-109
         const float shared_p = fmul(fadd(pressure, np), 0.5f);
-        tx = fdiv(fmul(fmul(dirx, k), shared_p), nd);
-        ty = fdiv(fmul(fmul(diry, k), shared_p), nd);
+        const float dvx = fsub(nv.x, vx), dvy = fsub(nv.y, vy);
+        const bool in_h = dst <= p.h;
+        const float k = in_h ? fmul(-fsub(p.h, dst), p.spiky) : 0.0f;  // funcs.wgsl:101-109
+        const float yr = rcp_refined(dst), yd = rcp_refined(nd);
+        const float dirx = div_by(dx, dst, yr), diry = div_by(dy, dst, yr);
+        const float tnx = fmul(fmul(dirx, k), shared_p), tny = fmul(fmul(diry, k), shared_p);
+        tx = div_by(tnx, nd, yd);
+        ty = div_by(tny, nd, yd);
+        const float r2 = fmul(dst, dst);
+        const float A = div_by(-fmul(r2, dst), p.two_h3, c.y_two_h3);
+        const float B = div_by(r2, p.h2, c.y_h2);
+        const float C = fmul(0.5f, div_by(p.h, dst, yr));  // h / (2 r): exact power-of-two scaling of h / r
+        const float kv = in_h ? fmul(p.visc_k, fsub(fadd(fadd(A, B), C), 1.0f)) : 0.0f;  // funcs.wgsl:112-123
+        ux = fmul(div_by(dvx, nd, yd), kv);  // compute.wgsl:288
+        uy = fmul(div_by(dvy, nd, yd), kv);
+        const int safe = (int)c.fast_div & (int)(sq >= DIV_DEN_LO * DIV_DEN_LO) & (int)(nd >= DIV_DEN_LO) &
+                         (int)(nd <= DIV_DEN_HI) & div_num_lo_ok(dx) & div_num_lo_ok(dy) & div_num_ok(dvx) &
+                         div_num_ok(dvy) & div_num_ok(tnx) & div_num_ok(tny);
+        if (!safe) {
+            float sdirx, sdiry;
+            if (dst == 0.0f) {  // compute.wgsl:211-212
+                const float rx = rand_f32(rand_seed);
+                const float ry = rand_f32(rand_seed);
+                const float len = fsqrt(fadd(fmul(rx, rx), fmul(ry, ry)));
+                sdirx = fdiv(rx, len); sdiry = fdiv(ry, len);
+            } else {
+                sdirx = fdiv(dx, dst); sdiry = fdiv(dy, dst);
+            }
+            tx = fdiv(fmul(fmul(sdirx, k), shared_p), nd);
+            ty = fdiv(fmul(fmul(sdiry, k), shared_p), nd);
+            const float skv = viscosity_kernel(p, dst);
+            ux = fmul(fdiv(dvx, nd), skv);
+            uy = fmul(fdiv(dvy, nd), skv);
+        }
         acc.px = fadd(acc.px, tx);
         acc.py = fadd(acc.py, ty);
-        const float kv = viscosity_kernel(p, dst);
-        ux = fmul(fdiv(fsub(nv.x, vx), nd), kv);  // compute.wgsl:288
-        uy = fmul(fdiv(fsub(nv.y, vy), nd), kv);
         acc.vx = fadd(acc.vx, ux);
         acc.vy = fadd(acc.vy, uy);
     } else {
@@ -333,6 +370,7 @@ __device__ __forceinline__ void force_walk_global(const DevParams& p, const floa
                                                   const uint32_t (&a)[3], const uint32_t (&b)[3], uint32_t self, float px,
                                                   float py, float vx, float vy, float pressure, uint32_t& rand_seed,
                                                   ForceAcc& acc) {
+    const PairConsts pc = make_pair_consts(p);
 #pragma unroll
     for (int r = 0; r < 3; r++) {
         for (uint32_t j = a[r]; j < b[r]; j++) {
@@ -341,7 +379,7 @@ __device__ __forceinline__ void force_walk_global(const DevParams& p, const floa
             const float dx = fsub(q.x, px), dy = fsub(q.y, py);
             const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
             if (sq > p.h2) continue;  // compute.wgsl:202 (sqr_radius == h*h)
-            force_pair<DEBUG, EXACT>(p, dx, dy, sq, vel[j], rho[j], vx, vy, pressure, rand_seed, acc);
+            force_pair<DEBUG, EXACT>(p, pc, dx, dy, sq, vel[j], rho[j], vx, vy, pressure, rand_seed, acc);
         }
     }
 }
@@ -361,6 +399,7 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
                                                   const int (&base)[3], const uint32_t (&a)[3], const uint32_t (&b)[3],
                                                   uint32_t self, float px, float py, float vx, float vy, float pressure,
                                                   uint32_t& rand_seed, ForceAcc& acc) {
+    const PairConsts pc = make_pair_consts(p);
     const uint32_t A1 = sp_addr + (a[1] - (uint32_t)base[1]) * 8u, E1 = sp_addr + (b[1] - (uint32_t)base[1]) * 8u;
     const uint32_t A2 = sp_addr + (a[2] - (uint32_t)base[2]) * 8u, E2 = sp_addr + (b[2] - (uint32_t)base[2]) * 8u;
     uint32_t addr = sp_addr + (a[0] - (uint32_t)base[0]) * 8u, end = sp_addr + (b[0] - (uint32_t)base[0]) * 8u;
@@ -400,7 +439,7 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
                 const float nd = lds_f(sr_addr + sidx * 4u);
                 const float dx = fsub(q.x, px), dy = fsub(q.y, py);
                 const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
-                force_pair<DEBUG, EXACT>(p, dx, dy, sq, nv, nd, vx, vy, pressure, rand_seed, acc);
+                force_pair<DEBUG, EXACT>(p, pc, dx, dy, sq, nv, nd, vx, vy, pressure, rand_seed, acc);
             }
         }
         __syncwarp();

@@ -268,6 +268,15 @@ int fluid_jfa_to_force_field(const uint32_t* seeds, uint32_t w, uint32_t h, floa
 int fluid_sim_jfa_from_particles(FluidSim* sim, uint32_t w, uint32_t h, uint32_t* seeds_out,
                                  float* field_xy_out, int into_sim, float* ms_out);
 
+/* ---- device self-tests ------------------------------------------------------------ */
+/* The exact-math force pass computes the 9 divisions of a neighbour pair (compute.wgsl:206-223, :283-288,
+ * funcs.wgsl:112-123) from shared, refined reciprocals. This sweeps every significand of the divisor at 13
+ * exponents with per_b numerators each and counts quotients that differ from the correctly rounded one
+ * (must be 0). inexact_reciprocals (optional) reports how many refined reciprocals differ from RN(1/b)
+ * (informational); first_bad (optional, 4 floats) = a, b, wanted, got of one mismatch. */
+int fluid_selftest_division(int device_ordinal, uint32_t seed, int per_b, uint64_t* tested, uint64_t* mismatches,
+                            uint64_t* inexact_reciprocals, float* first_bad);
+
 #ifdef __cplusplus
 }
 #endif
