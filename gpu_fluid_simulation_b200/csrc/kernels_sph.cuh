@@ -391,7 +391,51 @@ __device__ __forceinline__ void force_walk_global(const DevParams& p, const floa
 // per-thread list of up to FORCE_LIST entries, in visiting order; phase B evaluates the list in that
 // order. Visiting order, hence every fp32 sum, is unchanged. All shared accesses use explicit 32-bit
 // shared-window addresses so the loops carry no address arithmetic beyond one add.
-constexpr int FORCE_LIST = 16;
+#ifndef FLUID_FORCE_LIST
+#define FLUID_FORCE_LIST 16
+#endif
+#ifndef FLUID_FORCE_MIN_CTAS
+#define FLUID_FORCE_MIN_CTAS 1
+#endif
+constexpr int FORCE_LIST = FLUID_FORCE_LIST;
+
+// Phase-A inner loop, hand-scheduled: scans candidates [addr, end) of the staged predicted positions and appends
+// the shared-window address (its low 16 bits: static shared memory is < 64 KB) of every candidate with
+// !(r2 > h2) (compute.wgsl:202) to this thread's list column, until the span or the list is exhausted.
+// 13 instructions per candidate (was 19 through the compiler): LDS.64, 2 FADD, 2 FMUL, FADD, FSETP, predicated
+// STS + list bump, address bump, 2 ISETP, BRA.
+__device__ __forceinline__ void scan_span(uint32_t& addr, uint32_t end, uint32_t& wr, uint32_t wr_end, float px, float py,
+                                          float h2) {
+    asm volatile(
+        "{\n"
+        ".reg .pred hit, go;\n"
+        ".reg .f32 x, y, s;\n"
+        ".reg .b16 lo;\n"
+        "setp.lt.u32 go, %0, %2;\n"
+        "setp.lt.and.u32 go, %1, %3, go;\n"
+        "@!go bra SCAN_DONE;\n"
+        "SCAN_LOOP:\n"
+        "ld.shared.v2.f32 {x, y}, [%0];\n"
+        "sub.rn.f32 x, x, %4;\n"
+        "sub.rn.f32 y, y, %5;\n"
+        "mul.rn.f32 x, x, x;\n"
+        "mul.rn.f32 y, y, y;\n"
+        "add.rn.f32 s, x, y;\n"
+        "setp.leu.f32 hit, s, %6;\n"
+        "cvt.u16.u32 lo, %0;\n"
+        "@hit st.shared.u16 [%1], lo;\n"
+        "@hit add.u32 %1, %1, 512;\n"
+        "add.u32 %0, %0, 8;\n"
+        "setp.lt.u32 go, %0, %2;\n"
+        "setp.lt.and.u32 go, %1, %3, go;\n"
+        "@go bra SCAN_LOOP;\n"
+        "SCAN_DONE:\n"
+        "}\n"
+        : "+r"(addr), "+r"(wr)
+        : "r"(end), "r"(wr_end), "f"(px), "f"(py), "f"(h2)
+        : "memory");
+}
+static_assert(SPH_THREADS * 2 == 512, "scan_span hard-codes the list column stride");
 
 template <bool DEBUG, bool EXACT>
 __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t sp_addr, uint32_t sv_addr, uint32_t sr_addr,
@@ -400,31 +444,27 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
                                                   uint32_t self, float px, float py, float vx, float vy, float pressure,
                                                   uint32_t& rand_seed, ForceAcc& acc) {
     const PairConsts pc = make_pair_consts(p);
+    // four spans in visiting order: row y-1; row y before self; row y after self (compute.wgsl:195 skips self by
+    // index; a particle lies inside its own row's span unless the stale-entry quirk moved the span start past it); row y+1
+    const bool self_in = self >= a[1] && self < b[1];
     const uint32_t A1 = sp_addr + (a[1] - (uint32_t)base[1]) * 8u, E1 = sp_addr + (b[1] - (uint32_t)base[1]) * 8u;
+    const uint32_t S1 = self_in ? sp_addr + (self - (uint32_t)base[1]) * 8u : A1;  // end of the part before self
+    const uint32_t R1 = self_in ? S1 + 8u : A1;                                    // start of the part after self
     const uint32_t A2 = sp_addr + (a[2] - (uint32_t)base[2]) * 8u, E2 = sp_addr + (b[2] - (uint32_t)base[2]) * 8u;
     uint32_t addr = sp_addr + (a[0] - (uint32_t)base[0]) * 8u, end = sp_addr + (b[0] - (uint32_t)base[0]) * 8u;
-    const uint32_t self_addr = sp_addr + (self - (uint32_t)base[1]) * 8u;  // a particle lies in its own row's span
+    const uint32_t vel_delta = sv_addr - sp_addr, rho_base = sr_addr - (sp_addr >> 1);
+    const uint32_t wr_end = list_addr + FORCE_LIST * SPH_THREADS * 2u;
     int r = 0;
     bool more = true;
     while (__any_sync(0xffffffffu, more)) {
         uint32_t wr = list_addr;
-        const uint32_t wr_end = list_addr + FORCE_LIST * SPH_THREADS * 2u;
         // ---- phase A: scan ----
         while (more) {
-            while (addr < end && wr < wr_end) {  // tight inner loop
-                const float2 q = lds_f2(addr);
-                const float dx = fsub(q.x, px), dy = fsub(q.y, py);
-                const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
-                if (addr != self_addr && !(sq > p.h2)) {  // compute.wgsl:195, :202
-                    sts_u16(wr, (addr - sp_addr) >> 3);
-                    wr += SPH_THREADS * 2u;
-                }
-                addr += 8u;
-            }
+            scan_span(addr, end, wr, wr_end, px, py, p.h2);
             if (addr < end) break;  // list full: evaluate it, then resume this span
-            // next row span (constant indices keep a/b/base in registers)
-            if (r == 0) { addr = A1; end = E1; r = 1; }
-            else if (r == 1) { addr = A2; end = E2; r = 2; }
+            if (r == 0) { addr = A1; end = S1; r = 1; }
+            else if (r == 1) { addr = R1; end = E1; r = 2; }
+            else if (r == 2) { addr = A2; end = E2; r = 3; }
             else more = false;
         }
         __syncwarp();
@@ -433,10 +473,10 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
         const uint32_t max_bytes = __reduce_max_sync(0xffffffffu, cnt_bytes);
         for (uint32_t k = 0; k < max_bytes; k += SPH_THREADS * 2u) {
             if (k < cnt_bytes) {
-                const uint32_t sidx = lds_u16(list_addr + k);
-                const float2 q = lds_f2(sp_addr + sidx * 8u);
-                const float2 nv = lds_f2(sv_addr + sidx * 8u);
-                const float nd = lds_f(sr_addr + sidx * 4u);
+                const uint32_t e = lds_u16(list_addr + k);
+                const float2 q = lds_f2(e);
+                const float2 nv = lds_f2(e + vel_delta);
+                const float nd = lds_f((e >> 1) + rho_base);
                 const float dx = fsub(q.x, px), dy = fsub(q.y, py);
                 const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
                 force_pair<DEBUG, EXACT>(p, pc, dx, dy, sq, nv, nd, vx, vy, pressure, rand_seed, acc);
@@ -447,7 +487,7 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
 }
 
 template <bool DEBUG, bool EXACT>
-__global__ void __launch_bounds__(SPH_THREADS)
+__global__ void __launch_bounds__(SPH_THREADS, FLUID_FORCE_MIN_CTAS)
 k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const float2* __restrict__ pred_s,
                   const float2* __restrict__ vel_s, const float* __restrict__ rho, const uint32_t* __restrict__ keys,
                   const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk,
