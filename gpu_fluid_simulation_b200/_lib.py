@@ -104,6 +104,8 @@ PROTOTYPES = {
     "fluid_slab_configure": (_i, [_P, _i, _i, _P, _u32, _u32, _u32]),
     "fluid_slab_view": (_i, [_P, C.POINTER(SlabView)]),
     "fluid_slab_begin_tick": (_i, [_P, C.POINTER(TickSettingsC)]),
+    "fluid_slab_pack": (_i, [_P, _u32, _P]),
+    "fluid_slab_unpack": (_i, [_P, _P, _u32, _u32]),
     "fluid_slab_sort": (_i, [_P, _u32, _u32, _u32]),
     "fluid_slab_cells_density": (_i, [_P, _u32, _u32, _u32, _u32, _u32]),
     "fluid_slab_force": (_i, [_P]),

@@ -5,6 +5,7 @@
 // and one CUDA stream, and enqueues the per-tick kernel sequence
 //   predict+key+histogram -> scan -> onesweep x P -> gather+cell tables -> density -> force+integrate
 // in place of the reference's K1, K2, K3 x S(S+1)/2, K4, K5, K6 dispatches (src/simulation.rs:512-537).
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstring>

@@ -30,7 +30,8 @@ __global__ void __launch_bounds__(HASH_THREADS)
 k_slab_key_hist(const DevParams p, const float2* __restrict__ pos, const float2* __restrict__ vel, uint32_t count,
                 uint32_t* __restrict__ keys, uint32_t* __restrict__ g_hist, const SlabRows rows, int detect_emigrants,
                 uint32_t list_index_base, unsigned long long* __restrict__ emig_list, uint32_t* __restrict__ emig_count,
-                uint32_t emig_cap, uint32_t sentinel_key, uint32_t* __restrict__ frame_time) {
+                uint32_t* __restrict__ emig_dest_count, uint32_t emig_cap, uint32_t sentinel_key,
+                uint32_t* __restrict__ frame_time) {
     __shared__ uint32_t s_hist[PASSES * RADIX];
     for (int i = threadIdx.x; i < PASSES * RADIX; i += HASH_THREADS) s_hist[i] = 0;
     __syncthreads();
@@ -50,6 +51,7 @@ k_slab_key_hist(const DevParams p, const float2* __restrict__ pos, const float2*
 #pragma unroll 1
                     for (int r = 0; r < rows.world; r++) if (row >= rows.bounds[r]) dest = r;
                     const uint32_t slot = atomicAdd(emig_count, 1u);
+                    atomicAdd(emig_dest_count + dest, 1u);
                     if (slot < emig_cap) emig_list[slot] = ((unsigned long long)dest << 32) | (unsigned long long)(list_index_base + i);
                     k = sentinel_key;
                 }
@@ -97,7 +99,10 @@ __global__ void k_slab_halo_keys(const DevParams p, const float2* __restrict__ p
 // (compute.wgsl:45-56: global particle 0 writes nothing); cell_lb holds local (extended) indices.
 __global__ void __launch_bounds__(GATHER_THREADS)
 k_slab_build_cells(const DevParams p, const uint32_t* __restrict__ keys_ext, uint32_t* __restrict__ start_indices,
-                   uint32_t* __restrict__ cell_lb, uint32_t* __restrict__ quirk, uint32_t quirk_c0, uint32_t quirk_stale) {
+                   uint32_t* __restrict__ cell_lb, uint32_t* __restrict__ quirk, uint32_t quirk_c0, uint32_t quirk_stale,
+                   uint32_t fill_lo, uint32_t fill_hi) {
+    // [fill_lo, fill_hi): the table entries the neighbour passes of this band can read (rows row_first-1 .. row_end+1);
+    // gaps outside it (half the grid for an edge particle of a 2-rank split) are not filled
     const uint32_t i = p.ext_begin + blockIdx.x * GATHER_THREADS + threadIdx.x;
     const bool valid = i < p.ext_end;
     uint32_t gap_begin = 0, gap_end = 0, gap_value = 0;
@@ -117,22 +122,26 @@ k_slab_build_cells(const DevParams p, const uint32_t* __restrict__ keys_ext, uin
             }
         }
     }
+    gap_begin = max(gap_begin, fill_lo);
+    gap_end = min(gap_end, fill_hi);
+    if (gap_end < gap_begin) gap_end = gap_begin;
     warp_fill_gaps(cell_lb, gap_begin, gap_end, gap_value);
     uint32_t tb = 0, te = 0;
     if (valid && i == p.ext_end - 1u) {
-        tb = min(__ldg(keys_ext + i), p.num_cells - 1u) + 1u;
-        te = p.num_cells + 1u;
+        tb = max(min(__ldg(keys_ext + i), p.num_cells - 1u) + 1u, fill_lo);
+        te = min(p.num_cells + 1u, fill_hi);
+        if (te < tb) te = tb;
     }
     if (__any_sync(0xffffffffu, te > tb)) warp_fill_gaps(cell_lb, tb, te, p.ext_end);
 }
 // an empty extended range still needs a valid (all-empty) table
-__global__ void k_slab_fill_table(uint32_t* __restrict__ cell_lb, uint32_t count, uint32_t value) {
+__global__ void k_slab_fill_table(uint32_t* __restrict__ cell_lb, uint32_t first, uint32_t count, uint32_t value) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < count) cell_lb[i] = value;
+    if (i < count) cell_lb[first + i] = value;
 }
 
-// meta[0] = owned particles in the band's first grid row, meta[1] = in its last grid row,
-// meta[2] = key of the first owned particle, meta[3] = this rank's start_indices entry for that key
+// meta[0] = owned particles, meta[1] = of them in the band's first grid row, meta[2] = in its last grid row,
+// meta[3] = key of the first owned particle, meta[4] = this rank's start_indices entry for that key
 __global__ void k_slab_meta(const uint32_t* __restrict__ keys_owned, uint32_t n, uint32_t grid_w, uint32_t row_first,
                             uint32_t row_last, const uint32_t* __restrict__ start_indices, uint32_t num_cells,
                             uint32_t* __restrict__ meta) {
@@ -148,11 +157,69 @@ __global__ void k_slab_meta(const uint32_t* __restrict__ keys_owned, uint32_t n,
         }
         res[t] = lo;
     }
-    meta[0] = res[0];
-    meta[1] = n - res[1];
+    meta[0] = n;
+    meta[1] = res[0];
+    meta[2] = n - res[1];
     const uint32_t k0 = n ? min(keys_owned[0], num_cells - 1u) : 0xffffffffu;
-    meta[2] = k0;
-    meta[3] = n ? start_indices[k0] : 0u;
+    meta[3] = k0;
+    meta[4] = n ? start_indices[k0] : 0u;
+}
+
+// ---- migration payload (phase 2) ------------------------------------------------------------------------
+// emigrant list entries are (destination << 32 | state index), appended with an atomic counter: sorting them
+// ascending groups them by destination in source order, which is what makes the stable key sort reproduce
+// the single-GPU tie order. One CTA sorts up to EMIG_SORT_MAX entries in shared memory (bitonic network).
+constexpr int EMIG_SORT_MAX = 4096;
+constexpr int EMIG_SORT_THREADS = 1024;
+__global__ void __launch_bounds__(EMIG_SORT_THREADS)
+k_emig_sort_small(unsigned long long* __restrict__ list, uint32_t m) {
+    __shared__ unsigned long long s[EMIG_SORT_MAX];
+    uint32_t cap = 2;
+    while (cap < m) cap <<= 1;
+    for (uint32_t i = threadIdx.x; i < cap; i += EMIG_SORT_THREADS) s[i] = i < m ? list[i] : ~0ull;
+    __syncthreads();
+    for (uint32_t k = 2; k <= cap; k <<= 1)
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t i = threadIdx.x; i < cap; i += EMIG_SORT_THREADS) {
+                const uint32_t l = i ^ j;
+                if (l > i) {
+                    const unsigned long long a = s[i], b = s[l];
+                    const bool up = (i & k) == 0;
+                    if ((a > b) == up) { s[i] = b; s[l] = a; }
+                }
+            }
+            __syncthreads();
+        }
+    for (uint32_t i = threadIdx.x; i < m; i += EMIG_SORT_THREADS) list[i] = s[i];
+}
+// one compare-exchange step of a global-memory bitonic network (lists longer than EMIG_SORT_MAX; `cap` = m
+// rounded up to a power of two, entries past m hold 0xff.. which sorts last)
+__global__ void k_emig_sort_step(unsigned long long* __restrict__ list, uint32_t cap, uint32_t k, uint32_t j) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t l = i ^ j;
+    if (i >= cap || l <= i) return;
+    const unsigned long long a = list[i], b = list[l];
+    const bool up = (i & k) == 0;
+    if ((a > b) == up) { list[i] = b; list[l] = a; }
+}
+// payload[t] = (pos, vel) of the t-th emigrant of the sorted list
+__global__ void k_emig_pack(const unsigned long long* __restrict__ list, uint32_t m, const float2* __restrict__ pos,
+                            const float2* __restrict__ vel, float4* __restrict__ payload) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= m) return;
+    const uint32_t idx = (uint32_t)(list[t] & 0xffffffffull);
+    const float2 a = pos[idx], b = vel[idx];
+    payload[t] = make_float4(a.x, a.y, b.x, b.y);
+}
+// immigrants: recv[0, nb) came from lower ranks -> state[first_below ...]; recv[nb, nb+na) from higher ranks -> state[first_above ...]
+__global__ void k_immig_unpack(const float4* __restrict__ recv, uint32_t nb, uint32_t na, uint32_t first_below,
+                               uint32_t first_above, float2* __restrict__ pos, float2* __restrict__ vel) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nb + na) return;
+    const float4 v = recv[t];
+    const uint32_t o = t < nb ? first_below + t : first_above + (t - nb);
+    pos[o] = make_float2(v.x, v.y);
+    vel[o] = make_float2(v.z, v.w);
 }
 
 }  // namespace fluid

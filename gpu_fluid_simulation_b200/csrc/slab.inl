@@ -20,7 +20,7 @@ static void launch_slab_hash(Sim* s, const DevParams& p, uint32_t begin, uint32_
     if (blocks > max_blocks) blocks = max_blocks;
     k_slab_key_hist<PASSES><<<blocks, HASH_THREADS, 0, s->stream>>>(
         p, s->pos_a + begin, s->vel_a + begin, count, s->keys_u + begin, s->sort_scratch, s->slab_rows, detect,
-        begin, s->emig_list, s->emig_count, s->emig_cap, s->num_cells, frame_time);
+        begin, s->emig_list, s->emig_count, s->emig_count + 8, s->emig_cap, s->num_cells, frame_time);
     s->launches++;
 }
 static void slab_hash(Sim* s, const DevParams& p, uint32_t begin, uint32_t count, int detect, uint32_t* frame_time) {
@@ -54,9 +54,9 @@ int fluid_slab_configure(FluidSim* h, int rank, int world, const uint32_t* row_b
     FLUID_CUDA(cudaMalloc(&s->keys_ext, ((size_t)capacity + 2u * pad + 64) * 4));
     FLUID_CUDA(cudaMemsetAsync(s->keys_ext, 0, ((size_t)capacity + 2u * pad + 64) * 4, s->stream));
     FLUID_CUDA(cudaMalloc(&s->emig_list, (size_t)emig_cap * 8));
-    FLUID_CUDA(cudaMalloc(&s->slab_meta, 64));
-    FLUID_CUDA(cudaMemsetAsync(s->slab_meta, 0, 64, s->stream));
-    s->emig_count = s->slab_meta + 8;  // meta words 0..3, emigrant counter at word 8
+    FLUID_CUDA(cudaMalloc(&s->slab_meta, 256));
+    FLUID_CUDA(cudaMemsetAsync(s->slab_meta, 0, 256, s->stream));
+    s->emig_count = s->slab_meta + 8;  // meta words 0..4, emigrant counter at word 8, per-destination counters at words 16..31
     s->emig_cap = emig_cap;
     s->slab = true;
     s->slab_pad = pad;
@@ -104,10 +104,50 @@ int fluid_slab_begin_tick(FluidSim* h, const FluidTickSettings* t) {
     s->mark("begin");
     const uint32_t max_tiles = (s->slab_capacity + 2u * s->slab_pad + SORT_TILE - 1) / SORT_TILE;
     FLUID_CUDA(cudaMemsetAsync(s->sort_scratch, 0, ((size_t)MAX_PASSES * RADIX + RADIX + (size_t)s->sort_passes * max_tiles * RADIX) * 4, s->stream));
-    FLUID_CUDA(cudaMemsetAsync(s->emig_list, 0xff, (size_t)s->emig_cap * 8, s->stream));
-    FLUID_CUDA(cudaMemsetAsync(s->emig_count, 0, 4, s->stream));
+    FLUID_CUDA(cudaMemsetAsync(s->emig_count, 0, (8 + SLAB_MAX_RANKS) * 4, s->stream));
     slab_hash(s, s->slab_params, s->state_off, s->n, 1, s->d_frame_time);
     s->mark("predict+key+hist");
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+
+// phase 2a: sort the emigrant list (destination, then source order) and gather the payload
+int fluid_slab_pack(FluidSim* h, uint32_t n_emigrants, float* payload_dev) {
+    SLAB_OR_FAIL(h);
+    if (n_emigrants > s->emig_cap) { set_error("fluid_slab_pack: more emigrants than emig_cap"); return FLUID_ERR_INVALID_ARGUMENT; }
+    if (n_emigrants == 0) return FLUID_OK;
+    if (!payload_dev) { set_error("fluid_slab_pack: null payload"); return FLUID_ERR_INVALID_ARGUMENT; }
+    if (n_emigrants <= (uint32_t)EMIG_SORT_MAX) {
+        k_emig_sort_small<<<1, EMIG_SORT_THREADS, 0, s->stream>>>(s->emig_list, n_emigrants);
+        s->launches++;
+    } else {
+        uint32_t cap = 2;
+        while (cap < n_emigrants) cap <<= 1;
+        if (cap > s->emig_cap) { set_error("fluid_slab_pack: emig_cap must cover the next power of two of the emigrant count"); return FLUID_ERR_INVALID_ARGUMENT; }
+        FLUID_CUDA(cudaMemsetAsync(s->emig_list + n_emigrants, 0xff, (size_t)(cap - n_emigrants) * 8, s->stream));
+        for (uint32_t k = 2; k <= cap; k <<= 1)
+            for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                k_emig_sort_step<<<(cap + 255) / 256, 256, 0, s->stream>>>(s->emig_list, cap, k, j);
+                s->launches++;
+            }
+    }
+    k_emig_pack<<<(n_emigrants + 255) / 256, 256, 0, s->stream>>>(s->emig_list, n_emigrants, s->pos_a, s->vel_a,
+                                                                   reinterpret_cast<float4*>(payload_dev));
+    s->launches++;
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+
+// phase 2b: immigrants (ordered by source rank) into the slots around the natives
+int fluid_slab_unpack(FluidSim* h, const float* recv_dev, uint32_t n_from_below, uint32_t n_from_above) {
+    SLAB_OR_FAIL(h);
+    if (n_from_below > s->slab_pad || n_from_above > s->slab_pad) { set_error("fluid_slab_unpack: more immigrants than the pad holds"); return FLUID_ERR_INVALID_ARGUMENT; }
+    const uint32_t total = n_from_below + n_from_above;
+    if (total == 0) return FLUID_OK;
+    if (!recv_dev) { set_error("fluid_slab_unpack: null buffer"); return FLUID_ERR_INVALID_ARGUMENT; }
+    k_immig_unpack<<<(total + 255) / 256, 256, 0, s->stream>>>(reinterpret_cast<const float4*>(recv_dev), n_from_below, n_from_above,
+                                                               s->state_off - n_from_below, s->state_off + s->n, s->pos_a, s->vel_a);
+    s->launches++;
     FLUID_CUDA(cudaGetLastError());
     return FLUID_OK;
 }
@@ -183,11 +223,15 @@ int fluid_slab_cells_density(FluidSim* h, uint32_t halo_below, uint32_t halo_abo
         s->launches++;
     }
     const uint32_t ext = p.ext_end - p.ext_begin;
+    // table entries the neighbour passes of this band can read: rows row_first-1 .. row_end (+ the entry that ends row_end)
+    const uint32_t brow0 = s->slab_rows.bounds[s->slab_rows.rank], brow1 = s->slab_rows.bounds[s->slab_rows.rank + 1];
+    const uint32_t fill_lo = (brow0 > 0 ? brow0 - 1u : 0u) * s->grid_w;
+    const uint32_t fill_hi = (uint32_t)std::min<uint64_t>((uint64_t)(brow1 + 1u) * s->grid_w + 1u, (uint64_t)s->num_cells + 1u);
     if (ext) {
         k_slab_build_cells<<<(ext + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
-            p, s->keys_ext, s->start_indices, s->cell_lb, s->quirk, quirk_c0, quirk_stale_ext);
-    } else {
-        k_slab_fill_table<<<(s->num_cells + 1 + 255) / 256, 256, 0, s->stream>>>(s->cell_lb, s->num_cells + 1, p.ext_begin);
+            p, s->keys_ext, s->start_indices, s->cell_lb, s->quirk, quirk_c0, quirk_stale_ext, fill_lo, fill_hi);
+    } else if (fill_hi > fill_lo) {
+        k_slab_fill_table<<<(fill_hi - fill_lo + 255) / 256, 256, 0, s->stream>>>(s->cell_lb, fill_lo, fill_hi - fill_lo, p.ext_begin);
     }
     s->launches++;
     s->mark("cells");

@@ -79,7 +79,8 @@ class SlabRank:
         self.vel_sorted = _view(v.vel_sorted, (total, 2), "<f4", dv)
         self.rho = _view(v.rho, (total,), "<f4", dv)
         self.emig_list = _view(v.emig_list, (self.emig_cap,), "<i8", dv)
-        self.meta = _view(v.meta, (16,), "<i4", dv)  # words 0..3 band metadata, word 8 emigrant counter
+        self.meta = _view(v.meta, (64,), "<i4", dv)  # words 0..4 band metadata, word 8 emigrant counter, 16.. per destination
+        self.dest_counts = self.meta[16:16 + world]
         self.stream = torch.cuda.ExternalStream(self.sim.stream, device=dv)
         self.n = 0
         self.n_emig = 0
@@ -114,27 +115,22 @@ class SlabRank:
         _lib.check(self.lib.fluid_slab_begin_tick(self.h, C.byref(c)))
 
     def send_counts(self) -> torch.Tensor:
-        """int64[world] on the device: emigrants per destination rank (no host sync)."""
+        """int64[world] on the device: emigrants per destination rank, counted by the key pass (no host sync)."""
         with torch.cuda.stream(self.stream):
-            # entries are (dest << 32 | index): ascending order = grouped by destination, source order inside a group
-            self._sorted_list = torch.sort(self.emig_list).values
-            valid = self._sorted_list >= 0  # unused slots hold 0xff.. = -1
-            dest = torch.where(valid, self._sorted_list >> 32, torch.full_like(self._sorted_list, self.world))
-            return torch.bincount(dest, minlength=self.world + 1)[: self.world].contiguous()
+            return self.dest_counts.to(torch.int64)
 
     def pack(self, send_counts_host):
-        """payload float32[m, 4] = (pos, vel) of the emigrants grouped by destination, source order inside a group."""
+        """payload float32[m, 4] = (pos, vel) of the emigrants grouped by destination, source order inside a group
+        (the library sorts the emigrant list and gathers the payload)."""
         m = int(sum(send_counts_host))
         self.n_emig = m
         if m > self.emig_cap:
             raise _lib.FluidError(f"rank {self.rank}: {m} emigrants exceed emig_cap {self.emig_cap}")
         with torch.cuda.stream(self.stream):
-            if m == 0:
-                return torch.empty((0, 4), dtype=torch.float32, device=self.device)
-            # unused slots (0xff.. = -1 as int64) sort first: the m valid entries are the LAST m of the ascending list
-            lst = self._sorted_list[self.emig_cap - m:]
-            idx = lst & 0xFFFFFFFF
-            return torch.cat([self.pos_state[idx], self.vel_state[idx]], dim=1).contiguous()
+            payload = torch.empty((m, 4), dtype=torch.float32, device=self.device)
+            if m:
+                _lib.check(self.lib.fluid_slab_pack(self.h, m, _lib.ptr(payload)))
+            return payload
 
     # ---- phase 2: immigrants in -------------------------------------------------------------------------------
     def unpack(self, recv: torch.Tensor, recv_counts_host):
@@ -144,14 +140,10 @@ class SlabRank:
         if nb > self.pad or na > self.pad:
             raise _lib.FluidError(f"rank {self.rank}: {nb}+{na} immigrants exceed the pad {self.pad}")
         self.n_below, self.n_above = nb, na
-        P, n = self.pad, self.n
-        with torch.cuda.stream(self.stream):
-            if nb:
-                self.pos_state[P - nb:P] = recv[:nb, 0:2]
-                self.vel_state[P - nb:P] = recv[:nb, 2:4]
-            if na:
-                self.pos_state[P + n:P + n + na] = recv[nb:nb + na, 0:2]
-                self.vel_state[P + n:P + n + na] = recv[nb:nb + na, 2:4]
+        if nb + na:
+            recv = recv.contiguous()
+            _lib.check(self.lib.fluid_slab_unpack(self.h, _lib.ptr(recv), nb, na))
+            self._recv_keepalive = recv  # the copy kernel is only enqueued
 
     # ---- phases 3+4: sort, gather, metadata ---------------------------------------------------------------------
     def sort(self):
@@ -161,8 +153,7 @@ class SlabRank:
     def meta_tensor(self) -> torch.Tensor:
         """int64[5] on the device: n_owned, first-row count, last-row count, key of first owned, its table entry."""
         with torch.cuda.stream(self.stream):
-            m = self.meta[:4].to(torch.int64) & 0xFFFFFFFF
-            return torch.cat([torch.tensor([self.n], dtype=torch.int64, device=self.device), m])
+            return self.meta[:5].to(torch.int64) & 0xFFFFFFFF
 
     # ---- phase 5: halo rows ------------------------------------------------------------------------------------------
     def halo_out(self, first_count, last_count):
@@ -291,29 +282,51 @@ class DistDriver:
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.exchange_bytes = 0
+        self.profile = None  # dict name -> seconds when section profiling is on (scripts/slab_profile.py); serialises the step
+
+    def _section(self, name):
+        if self.profile is None:
+            return
+        import time
+        torch.cuda.synchronize()
+        now = time.perf_counter()
+        self.profile[name] = self.profile.get(name, 0.0) + now - self._t_last
+        self._t_last = now
 
     def tick(self, ts: TickSettings):
         dist, r, W, me = self.dist, self.r, self.world, self.rank
+        if self.profile is not None:
+            import time
+            torch.cuda.synchronize()
+            self._t_last = time.perf_counter()
         with r.stream_ctx():
             r.begin_tick(ts)
+            self._section("begin_tick")
             # ---- migration: counts, then payload ----
             sc = r.send_counts()
             rc = torch.empty_like(sc)
+            self._section("send_counts")
             dist.all_to_all_single(rc, sc, group=self.group)
             both = torch.stack([sc, rc]).cpu().numpy()  # synchronises
             send_counts, recv_counts = both[0], both[1]
+            self._section("a2a_counts+host")
             payload = r.pack(send_counts)
+            self._section("pack")
             recv = torch.empty((int(recv_counts.sum()), 4), dtype=torch.float32, device=r.device)
             if int(send_counts.sum()) or int(recv_counts.sum()) or True:
                 dist.all_to_all_single(recv, payload, output_split_sizes=[int(x) for x in recv_counts],
                                        input_split_sizes=[int(x) for x in send_counts], group=self.group)
+            self._section("a2a_payload")
             r.unpack(recv, recv_counts)
+            self._section("unpack")
             r.sort()
+            self._section("sort")
             # ---- band metadata of every rank ----
             m = r.meta_tensor()
             allm = torch.empty(W * m.numel(), dtype=m.dtype, device=r.device)
             dist.all_gather_into_tensor(allm, m, group=self.group)
             metas = allm.view(W, -1).cpu().numpy()  # synchronises
+            self._section("metas")
             prefix = np.concatenate([[0], np.cumsum(metas[:, 0])])
             c0, stale = _quirk_from_metas(metas)
             # ---- halo rows of (pred, vel) ----
@@ -332,7 +345,9 @@ class DistDriver:
             if ops:
                 for w in dist.batch_isend_irecv(ops):
                     w.wait()
+            self._section("halo_exchange")
             r.cells_density(int(prefix[me]), c0, stale)
+            self._section("cells_density")
             # ---- halo rho ----
             ro_b, ro_a = r.rho_out()
             ri_b, ri_a = r.rho_in()
@@ -348,7 +363,9 @@ class DistDriver:
             if ops:
                 for w in dist.batch_isend_irecv(ops):
                     w.wait()
+            self._section("rho_exchange")
             r.force()
+            self._section("force")
         self.last_metas = metas
         self.exchange_bytes = int(16 * (send_counts.sum() + recv_counts.sum()) + 20 * (r.halo_below + r.halo_above + r._first + r._last))
 

@@ -225,8 +225,8 @@ typedef struct FluidSlabView {
     void* rho;             /* float[...] */
     void* keys_ext;        /* uint32[...] */
     void* emig_list;       /* uint64[emig_cap]: (destination rank << 32) | index into the state arrays; 0xff.. = unused */
-    void* emig_count;      /* uint32 */
-    void* meta;            /* uint32[4]: first-row count, last-row count, key of first owned, its start_indices entry */
+    void* emig_count;      /* uint32; emig_count[8 + r] = emigrants bound for rank r */
+    void* meta;            /* uint32[5]: n owned, first-row count, last-row count, key of first owned, its start_indices entry */
     void* start_indices;   /* uint32[grid_w*grid_h], global sorted indices for the cells this rank owns */
 } FluidSlabView;
 int fluid_slab_configure(FluidSim* sim, int rank, int world, const uint32_t* row_bounds /* world+1 */, uint32_t capacity,
@@ -234,6 +234,11 @@ int fluid_slab_configure(FluidSim* sim, int rank, int world, const uint32_t* row
 int fluid_slab_view(FluidSim* sim, FluidSlabView* out);
 /* phase 1: tick += 1; keys of the natives; emigrants listed and given the sentinel key */
 int fluid_slab_begin_tick(FluidSim* sim, const FluidTickSettings* tick);
+/* phase 2a: sort the emigrant list (destination rank, then source order) and gather (pos, vel) of the n_emigrants
+ * into payload_dev (DEVICE pointer, float[n_emigrants*4]); 2b: place the received immigrants (DEVICE pointer,
+ * ordered by source rank: n_from_below then n_from_above records) around the natives */
+int fluid_slab_pack(FluidSim* sim, uint32_t n_emigrants, float* payload_dev);
+int fluid_slab_unpack(FluidSim* sim, const float* recv_dev, uint32_t n_from_below, uint32_t n_from_above);
 /* phase 3+4: keys of the immigrants (already copied in around the natives), sort, gather, band metadata */
 int fluid_slab_sort(FluidSim* sim, uint32_t n_from_below, uint32_t n_from_above, uint32_t n_emigrants);
 /* phase 6+7a: halo keys, cell tables, density. quirk_*: lowest occupied cell of the whole domain and its stale
