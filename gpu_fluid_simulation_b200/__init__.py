@@ -6,4 +6,4 @@ the Python host mirror of the reference interface; it never falls back to a CPU 
 """
 from ._lib import PARTICLE_DTYPE, FluidError, load  # noqa: F401
 from .simulation import FluidSimulation, SimulationSettings, TickSettings  # noqa: F401
-from . import jfa, scenes  # noqa: F401
+from . import field, jfa, scenes  # noqa: F401

@@ -16,6 +16,9 @@ PARTICLE_DTYPE = np.dtype([
     ("position", np.float32, 2), ("predicted_position", np.float32, 2), ("velocity", np.float32, 2),
     ("density", np.float32), ("grid", np.uint32)], align=False)
 assert PARTICLE_DTYPE.itemsize == 32
+# reference FluidObject (src/renderer.rs:82-90): pad / pad2 carry bit-cast floats
+OBJECT_DTYPE = np.dtype([("position", np.float32, 2), ("kind", np.uint32), ("pad", np.uint32), ("pad2", np.uint32, 4)], align=False)
+assert OBJECT_DTYPE.itemsize == 32
 
 
 class SimSettings(C.Structure):
@@ -115,6 +118,9 @@ PROTOTYPES = {
     "fluid_jfa_seed_from_particles": (_i, [_P, _u32, C.POINTER(C.c_float * 2), _u32, _u32, _P, _i]),
     "fluid_jfa_to_force_field": (_i, [_P, _u32, _u32, _P, _i]),
     "fluid_sim_jfa_from_particles": (_i, [_P, _u32, _u32, _P, _P, _i, C.POINTER(C.c_float)]),
+    "fluid_raster_objects": (_i, [_P, _u32, _P, _u32, _u32, _P, _i]),
+    "fluid_sim_field_from_objects": (_i, [_P, _P, _u32, _P, _P, _P, _P, C.POINTER(C.c_float)]),
+    "fluid_sim_field_from_mask": (_i, [_P, _P, _P, _P, C.POINTER(C.c_float)]),
     "fluid_selftest_division": (_i, [_i, _u32, _i, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),
                                      C.POINTER(C.c_float)]),
 }

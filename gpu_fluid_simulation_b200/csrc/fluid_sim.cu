@@ -379,7 +379,8 @@ void fluid_sim_destroy(FluidSim* h) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
                     s->idx_b, s->sort_scratch, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
-                    s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta};
+                    s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta,
+                    s->mask_dev, s->mask_flag, s->objects_dev};
     for (void* b : bufs) if (b) cudaFree(b);
     for (auto& row : s->mark_events) for (auto& e : row) if (e) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);

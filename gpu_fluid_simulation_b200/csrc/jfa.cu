@@ -448,3 +448,5 @@ int fluid_sim_jfa_from_particles(FluidSim* h_, uint32_t w, uint32_t h, uint32_t*
 }
 
 }  // extern "C"
+
+#include "field.inl"

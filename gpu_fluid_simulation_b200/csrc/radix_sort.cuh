@@ -38,8 +38,18 @@ __global__ void __launch_bounds__(RADIX) k_scan_histograms(uint32_t* __restrict_
     hp[threadIdx.x] = base + incl - v;
 }
 
+// tuning (scripts/sweep_force.sh, 64M-U, ms for the 3 passes): batch 1/4/8/16 at 4 CTAs per SM = 1.15 / 1.01 / 1.04 / 1.11;
+// unbounded registers (1 CTA per SM) = 2.2; 5 or 6 CTAs per SM or 8 / 12 / 24 keys per thread are all slower
+#ifndef FLUID_LOOKBACK_BATCH
+#define FLUID_LOOKBACK_BATCH 4
+#endif
+#ifndef FLUID_SORT_MIN_CTAS
+#define FLUID_SORT_MIN_CTAS 4
+#endif
+constexpr int LOOKBACK_BATCH = FLUID_LOOKBACK_BATCH;
+
 template <int ITEMS, bool IDENTITY_VALUES>
-__global__ void __launch_bounds__(SORT_THREADS)
+__global__ void __launch_bounds__(SORT_THREADS, FLUID_SORT_MIN_CTAS)
 k_onesweep_pass(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                 uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out,
                 const uint32_t* __restrict__ digit_base,  // [256] exclusive-scanned global histogram of this digit
@@ -133,15 +143,28 @@ k_onesweep_pass(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict
     }
 
     // ---- decoupled look-back for digit `tid` (overlaps the smem scatter of the other warps) ----
+    // Predecessor status words are fetched LOOKBACK_BATCH at a time (independent loads, one L2 round trip per batch)
+    // and consumed in order: with ~600 resident tiles in near lock step the nearest tile holding an inclusive prefix
+    // is typically tens of tiles back, and a one-load-at-a-time walk serialises that many ~1 us L2 round trips.
     uint32_t excl = 0;
     if (tile > 0) {
         int t = (int)tile - 1;
-        while (true) {
-            uint32_t s;
-            do { s = tile_status[(size_t)t * RADIX + tid]; } while ((s >> 30) == 0u);
-            excl += s & STATUS_VALUE_MASK;
-            if ((s >> 30) == 2u) break;
-            t--;
+        bool done = false;
+        while (!done) {
+            uint32_t sw[LOOKBACK_BATCH];
+#pragma unroll
+            for (int j = 0; j < LOOKBACK_BATCH; j++)
+                sw[j] = (t - j >= 0) ? tile_status[(size_t)(t - j) * RADIX + tid] : 0x80000000u;  // before tile 0: inclusive prefix 0
+#pragma unroll
+            for (int j = 0; j < LOOKBACK_BATCH; j++) {
+                if (!done) {
+                    uint32_t v = sw[j];
+                    while ((v >> 30) == 0u) v = tile_status[(size_t)(t - j) * RADIX + tid];
+                    excl += v & STATUS_VALUE_MASK;
+                    if ((v >> 30) == 2u) done = true;
+                }
+            }
+            t -= LOOKBACK_BATCH;
         }
         my_status[tid] = STATUS_FLAG_INCL | (excl + count);
     }

@@ -5,7 +5,10 @@
 
 namespace fluid {
 
-constexpr int SORT_ITEMS = 16;                          // keys per thread per onesweep tile
+#ifndef FLUID_SORT_ITEMS
+#define FLUID_SORT_ITEMS 16
+#endif
+constexpr int SORT_ITEMS = FLUID_SORT_ITEMS;                          // keys per thread per onesweep tile
 constexpr uint32_t SORT_TILE = SORT_THREADS * SORT_ITEMS;
 constexpr int MAX_MARKS = 12;
 constexpr int TIMING_RING = 256;
@@ -59,6 +62,10 @@ struct Sim {
 
     uint32_t *jfa_a = nullptr, *jfa_b = nullptr;  // packed seed ping-pong for fluid_sim_jfa_from_particles
     size_t jfa_pixels = 0;
+    uint8_t* mask_dev = nullptr;                  // obstacle mask at texture size (field.inl)
+    uint32_t* mask_flag = nullptr;
+    void* objects_dev = nullptr;                  // prepared FluidObjects
+    uint32_t objects_cap = 0;
 
     // per-phase device timing: a ring of TIMING_RING ticks x MAX_MARKS events on `stream`
     bool timing = false;

@@ -273,6 +273,31 @@ int fluid_jfa_to_force_field(const uint32_t* seeds, uint32_t w, uint32_t h, floa
 int fluid_sim_jfa_from_particles(FluidSim* sim, uint32_t w, uint32_t h, uint32_t* seeds_out,
                                  float* field_xy_out, int into_sim, float* ms_out);
 
+/* ---- obstacle objects -> mask -> seeds -> JFA -> force field ----------------
+ * FluidObject = the reference's storage-buffer record (src/renderer.rs:82-90, image_shader.wgsl:6-11):
+ * kind 0 = circle, radius = bitcast<f32>(pad); kind 1 = rectangle, rotation = bitcast<f32>(pad),
+ * extents = bitcast<vec2<f32>>(pad2.xy). inv_proj = the inverse projection of ObjectUniform
+ * (src/renderer.rs:72-79, :449-453), 16 floats, column-major (glam Mat4). Mask: u8, 0 inside an object,
+ * 255 elsewhere (image_shader.wgsl:41-67), row 0 = top of the framebuffer. */
+typedef struct FluidObject {
+    float position[2];
+    uint32_t kind;
+    uint32_t pad;
+    uint32_t pad2[4];
+} FluidObject;
+/* mask only, HOST buffers: mirrors the reference's object render pass + texture readback. */
+int fluid_raster_objects(const FluidObject* objects, uint32_t n, const float inv_proj[16], uint32_t w, uint32_t h,
+                         uint8_t* mask_out, int device_ordinal);
+/* Device-resident pipeline at the sim's texture size: rasterise -> seed rule of src/main.rs:413-438 -> JFA ->
+ * field installed as the sim's force field (what src/renderer.rs:497-547 does through a readback, a CPU thread
+ * running generate_smooth_gradient_field and an 8 MiB upload, one or more frames late). Optional host outputs
+ * (any may be NULL): mask (w*h u8), seeds (w*h rg32uint), field (w*h float pairs), device ms of the chain.
+ * With every output NULL the call only enqueues work on the sim's stream. */
+int fluid_sim_field_from_objects(FluidSim* sim, const FluidObject* objects, uint32_t n, const float inv_proj[16],
+                                 uint8_t* mask_out, uint32_t* seeds_out, float* field_xy_out, float* ms_out);
+/* the same from a caller-supplied u8 mask at texture size (the reference's `Image`, src/main.rs:379-399). */
+int fluid_sim_field_from_mask(FluidSim* sim, const uint8_t* mask, uint32_t* seeds_out, float* field_xy_out, float* ms_out);
+
 /* ---- device self-tests ------------------------------------------------------------ */
 /* The exact-math force pass computes the 9 divisions of a neighbour pair (compute.wgsl:206-223, :283-288,
  * funcs.wgsl:112-123) from shared, refined reciprocals. This sweeps every significand of the divisor at 13

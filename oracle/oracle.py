@@ -45,8 +45,8 @@ class Uniform(C.Structure):
 
 
 def build(force=False):
-    src = os.path.join(HERE, "fluid_oracle.cpp")
-    if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < os.path.getmtime(src):
+    srcs = [os.path.join(HERE, f) for f in ("fluid_oracle.cpp", "render_oracle.cpp")]
+    if force or not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < max(os.path.getmtime(f) for f in srcs):
         subprocess.run(["make", "-C", HERE, "-B", "liboracle.so"], check=True, capture_output=True)
     return LIB_PATH
 
@@ -250,6 +250,19 @@ def generate_smooth_gradient_field(mask, want_nearest=False):
     near = np.empty((h, w, 2), dtype=np.uint32) if want_nearest else None
     lib().oracle_generate_smooth_gradient_field(_p(mask), C.c_uint32(w), C.c_uint32(h), _p(out), _p(near))
     return (out, near) if want_nearest else out
+
+
+# ---- per-pixel shaders (render_oracle.cpp) ------------------------------------------------------------
+OBJECT_DTYPE = np.dtype([("position", np.float32, 2), ("kind", np.uint32), ("pad", np.uint32), ("pad2", np.uint32, 4)], align=False)
+
+
+def rasterize_objects(objects, inv_proj, w, h):
+    """image_shader.wgsl fs_main -> u8 mask (0 inside an object, 255 elsewhere)."""
+    objects = np.ascontiguousarray(objects, dtype=OBJECT_DTYPE)
+    m = np.ascontiguousarray(inv_proj, dtype=np.float32).reshape(16)
+    out = np.empty((h, w), dtype=np.uint8)
+    lib().oracle_rasterize_objects(_p(objects), C.c_uint32(objects.shape[0]), _p(m), C.c_uint32(w), C.c_uint32(h), _p(out))
+    return out
 
 
 def bruteforce_density_f64(u, p):
