@@ -87,3 +87,14 @@ def field_from_mask(sim, mask: np.ndarray, want_seeds=False, want_field=False, t
     _lib.check(sim._lib.fluid_sim_field_from_mask(sim._h, _lib.ptr(mask), _lib.ptr(seeds), _lib.ptr(field),
                                                  C.byref(ms) if timed else None))
     return seeds, field, (ms.value if timed else None)
+
+
+def render(sim, inv_proj, w: int = 960, h: int = 540, want_f32=True, want_rgba8=False, timed=False):
+    """headless fluid_shader.wgsl: returns (float32[h, w, 4] fragment output, uint8[h, w, 4] blended image, ms)."""
+    m = np.ascontiguousarray(inv_proj, dtype=np.float32).reshape(16)
+    f = np.empty((h, w, 4), dtype=np.float32) if want_f32 else None
+    b = np.empty((h, w, 4), dtype=np.uint8) if want_rgba8 else None
+    ms = C.c_float(0.0)
+    _lib.check(sim._lib.fluid_sim_render(sim._h, _lib.ptr(m), int(w), int(h), _lib.ptr(f), _lib.ptr(b),
+                                        C.byref(ms) if timed else None))
+    return f, b, (ms.value if timed else None)

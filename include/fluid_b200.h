@@ -298,6 +298,15 @@ int fluid_sim_field_from_objects(FluidSim* sim, const FluidObject* objects, uint
 /* the same from a caller-supplied u8 mask at texture size (the reference's `Image`, src/main.rs:379-399). */
 int fluid_sim_field_from_mask(FluidSim* sim, const uint8_t* mask, uint32_t* seeds_out, float* field_xy_out, float* ms_out);
 
+/* ---- headless fluid render --------------------------------------------------
+ * fluid_shader.wgsl fs_main (the live root copy, src/renderer.rs:162) evaluated per pixel of a w x h target
+ * (reference: RENDER_DIMS 960 x 540, src/renderer.rs:15) over the sim's sorted particles and start_indices
+ * table; inv_proj as for the objects. HOST outputs, either may be NULL: rgba_f32_out = the fragment's
+ * vec4<f32> (w*h*4 floats); rgba8_out = that fragment ALPHA_BLENDed over the cleared opaque-black target
+ * (src/renderer.rs:178, :437) as UNORM8 (w*h*4 bytes). Row 0 = top of the framebuffer. */
+int fluid_sim_render(FluidSim* sim, const float inv_proj[16], uint32_t w, uint32_t h, float* rgba_f32_out,
+                     uint8_t* rgba8_out, float* ms_out);
+
 /* ---- device self-tests ------------------------------------------------------------ */
 /* The exact-math force pass computes the 9 divisions of a neighbour pair (compute.wgsl:206-223, :283-288,
  * funcs.wgsl:112-123) from shared, refined reciprocals. This sweeps every significand of the divisor at 13

@@ -265,6 +265,14 @@ def rasterize_objects(objects, inv_proj, w, h):
     return out
 
 
+def render_fluid(u, p, table, inv_proj, w, h):
+    """fluid_shader.wgsl fs_main -> float32[h, w, 4] (the fragment output, before blending)."""
+    m = np.ascontiguousarray(inv_proj, dtype=np.float32).reshape(16)
+    out = np.empty((h, w, 4), dtype=np.float32)
+    lib().oracle_render_fluid(C.byref(u), _p(p), _p(table), _p(m), C.c_uint32(w), C.c_uint32(h), _p(out))
+    return out
+
+
 def bruteforce_density_f64(u, p):
     out = np.empty(p.shape[0], dtype=np.float64)
     lib().oracle_bruteforce_density_f64(C.byref(u), _p(p), _p(out))
