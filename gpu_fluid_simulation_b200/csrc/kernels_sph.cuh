@@ -171,21 +171,53 @@ __device__ __forceinline__ float density_walk_global(const DevParams& p, const f
     return density;
 }
 
-// staged: one iterator over the three row spans (the warp's trip count is the max over lanes of the SUM of
-// the span lengths, not the sum of the per-span maxima), explicit 32-bit shared addresses
+// Inner loop of the staged walk, hand-scheduled (15 instructions per candidate: LDS.64, 2 FADD, 2 FMUL, FADD, FSETP,
+// FADD + 4 FMUL of the kernel value computed unconditionally, the one predicated FADD into the sum, address bump,
+// ISETP, BRA). The compiler's version unrolled each span x4 / x2 / x1 with separate remainder loops, so lanes of a
+// warp sat in three different loops per span (ncu: 27.7 warp instructions per particle for ~36 candidates).
+// Tried and dropped (round 1): re-assigning particles to threads by neighbour count to even out the warps of the
+// force pass — with the scan it made the candidate walk diverge (5.7 -> 5.9 ms), with a scanner/evaluator split it
+// needed CTA-wide barriers per round (7.2 ms).
+__device__ __forceinline__ void density_span(uint32_t addr, uint32_t end, float px, float py, float h2, float norm, float mass,
+                                             float& density) {
+    asm volatile(
+        "{\n"
+        ".reg .pred in, go;\n"
+        ".reg .f32 x, y, s, d, k;\n"
+        "setp.lt.u32 go, %1, %2;\n"
+        "@!go bra DENS_DONE;\n"
+        "DENS_LOOP:\n"
+        ".pragma \"nounroll\";\n"       // ptxas would re-create the x4 / x2 / x1 remainder structure
+        "ld.shared.v2.f32 {x, y}, [%1];\n"
+        "sub.rn.f32 x, x, %3;\n"
+        "sub.rn.f32 y, y, %4;\n"
+        "mul.rn.f32 x, x, x;\n"
+        "mul.rn.f32 y, y, y;\n"
+        "add.rn.f32 s, x, y;\n"
+        "setp.leu.f32 in, s, %5;\n"      // funcs.wgsl:74: r2 > h2 -> 0; NaN falls through, as there
+        "sub.rn.f32 d, %5, s;\n"
+        "mul.rn.f32 k, %6, d;\n"         // funcs.wgsl:76: norm * d * d * d, left to right
+        "mul.rn.f32 k, k, d;\n"
+        "mul.rn.f32 k, k, d;\n"
+        "mul.rn.f32 k, %7, k;\n"         // funcs.wgsl:189-192: mass * kernel
+        "@in add.rn.f32 %0, %0, k;\n"
+        "add.u32 %1, %1, 8;\n"
+        "setp.lt.u32 go, %1, %2;\n"
+        "@go bra DENS_LOOP;\n"
+        "DENS_DONE:\n"
+        "}\n"
+        : "+f"(density), "+r"(addr)
+        : "r"(end), "f"(px), "f"(py), "f"(h2), "f"(norm), "f"(mass));
+}
+
+// staged: the three row spans in visiting order, explicit 32-bit shared addresses
 __device__ __forceinline__ float density_walk_staged(const DevParams& p, uint32_t sp_addr, const int (&base)[3],
                                                      const uint32_t (&a)[3], const uint32_t (&b)[3], float px, float py) {
     float density = 0.0f;
-    const uint32_t A1 = sp_addr + (a[1] - (uint32_t)base[1]) * 8u, E1 = sp_addr + (b[1] - (uint32_t)base[1]) * 8u;
-    const uint32_t A2 = sp_addr + (a[2] - (uint32_t)base[2]) * 8u, E2 = sp_addr + (b[2] - (uint32_t)base[2]) * 8u;
-    uint32_t addr = sp_addr + (a[0] - (uint32_t)base[0]) * 8u, end = sp_addr + (b[0] - (uint32_t)base[0]) * 8u;
-    int r = 0;
-    while (true) {
-        for (; addr < end; addr += 8u) density_candidate(p, lds_f2(addr), px, py, density);  // tight inner loop
-        if (r == 0) { addr = A1; end = E1; r = 1; }
-        else if (r == 1) { addr = A2; end = E2; r = 2; }
-        else break;
-    }
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+        density_span(sp_addr + (a[r] - (uint32_t)base[r]) * 8u, sp_addr + (b[r] - (uint32_t)base[r]) * 8u, px, py, p.h2,
+                     p.poly6_norm, p.mass, density);
     return density;
 }
 
