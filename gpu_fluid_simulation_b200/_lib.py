@@ -61,7 +61,8 @@ class SlabView(C.Structure):
     _fields_ = [("n", C.c_uint32), ("pad", C.c_uint32), ("capacity", C.c_uint32), ("emig_cap", C.c_uint32),
                 ("pos_state", C.c_void_p), ("vel_state", C.c_void_p), ("pos_sorted", C.c_void_p),
                 ("pred_sorted", C.c_void_p), ("vel_sorted", C.c_void_p), ("rho", C.c_void_p), ("keys_ext", C.c_void_p),
-                ("emig_list", C.c_void_p), ("emig_count", C.c_void_p), ("meta", C.c_void_p), ("start_indices", C.c_void_p)]
+                ("emig_list", C.c_void_p), ("emig_count", C.c_void_p), ("meta", C.c_void_p), ("start_indices", C.c_void_p),
+                ("dyn", C.c_void_p)]
 
 
 _P = C.c_void_p
@@ -111,6 +112,7 @@ PROTOTYPES = {
     "fluid_slab_unpack": (_i, [_P, _P, _u32, _u32]),
     "fluid_slab_sort": (_i, [_P, _u32, _u32, _u32]),
     "fluid_slab_cells_density": (_i, [_P, _u32, _u32, _u32, _u32, _u32]),
+    "fluid_slab_cells_density_dev": (_i, [_P, _P]),
     "fluid_slab_force": (_i, [_P]),
     "fluid_jfa_run": (_i, [_P, _u32, _u32, _P, _i]),
     "fluid_jfa_pass": (_i, [_P, _u32, _u32, _u32, _P, _i]),

@@ -192,7 +192,7 @@ void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, 
 #define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                     \
     k_force_integrate<DBG, EX><<<blocks, SPH_THREADS, 0, s->stream>>>(p, s->pos_s, s->pred_s, s->vel_s, s->rho, keys,   \
                                                                       s->cell_lb, s->quirk, s->force_field,             \
-                                                                      s->d_frame_time, pos_out, vel_out, da, db)
+                                                                      s->d_frame_time, s->slab_goff_dev, pos_out, vel_out, da, db)
     if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
     else { if (s->exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
 #undef FLUID_LAUNCH_FORCE
@@ -380,7 +380,7 @@ void fluid_sim_destroy(FluidSim* h) {
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
                     s->idx_b, s->sort_scratch, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
                     s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta,
-                    s->mask_dev, s->mask_flag, s->objects_dev};
+                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn};
     for (void* b : bufs) if (b) cudaFree(b);
     for (auto& row : s->mark_events) for (auto& e : row) if (e) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);

@@ -95,24 +95,86 @@ __global__ void k_slab_halo_keys(const DevParams p, const float2* __restrict__ p
     keys_ext[i] = cell_key(p, __ldg(pred_s + i));
 }
 
+// ---- device-resolved protocol: what the host used to read back between the sort and the cell tables --------------
+struct SlabDyn {
+    uint32_t hb, ha;             // halo particles below / above (the neighbours' last / first row counts)
+    uint32_t ext_begin, ext_end; // [halo | owned | halo] in the key-ordered arrays
+    uint32_t global_offset;      // particles on lower ranks
+    uint32_t quirk_c0, quirk_stale_ext;
+    uint32_t error;              // bit 0: a halo row is larger than the pad
+};
+constexpr uint32_t SLAB_META_WORDS = 8;  // per rank in the gathered array: n, first-row count, last-row count, first key, its table entry
+// one thread: every rank's band metadata (all_gather output, device resident) -> this rank's SlabDyn and quirk words
+__global__ void k_slab_resolve(const uint32_t* __restrict__ allmeta, int world, int me, uint32_t own_begin, uint32_t n,
+                               uint32_t pad, SlabDyn* __restrict__ dyn, uint32_t* __restrict__ quirk) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    uint32_t prefix = 0;
+    for (int r = 0; r < me; r++) prefix += allmeta[r * SLAB_META_WORDS];
+    uint32_t hb = me > 0 ? allmeta[(me - 1) * SLAB_META_WORDS + 2] : 0u;
+    uint32_t ha = me + 1 < world ? allmeta[(me + 1) * SLAB_META_WORDS + 1] : 0u;
+    uint32_t err = 0;
+    if (hb > pad) { hb = pad; err |= 1u; }
+    if (ha > pad) { ha = pad; err |= 1u; }
+    uint32_t c0 = 0xffffffffu, stale = 0;
+    for (int r = 0; r < world; r++)
+        if (allmeta[r * SLAB_META_WORDS] > 0u) { c0 = allmeta[r * SLAB_META_WORDS + 3]; stale = allmeta[r * SLAB_META_WORDS + 4]; break; }
+    const uint32_t ext_begin = own_begin - hb;
+    uint32_t stale_ext = 0;
+    if (c0 != 0xffffffffu) {  // the stale entry is a GLOBAL sorted index: translate into this rank's extended index space
+        long long t = (long long)stale - (long long)prefix + (long long)own_begin;
+        if (t < (long long)ext_begin) t = ext_begin;
+        if (t > 0xffffffffll) t = 0xffffffffll;
+        stale_ext = (uint32_t)t;
+    }
+    dyn->hb = hb; dyn->ha = ha; dyn->ext_begin = ext_begin; dyn->ext_end = own_begin + n + ha;
+    dyn->global_offset = prefix; dyn->quirk_c0 = c0; dyn->quirk_stale_ext = stale_ext;
+    dyn->error |= err;
+    quirk[0] = c0; quirk[1] = stale_ext;
+}
+// keys of the received halo particles; grid over 2 * pad threads, counts from SlabDyn
+__global__ void k_slab_halo_keys_dev(const DevParams p, const float2* __restrict__ pred_s, uint32_t* __restrict__ keys_ext,
+                                     const SlabDyn* __restrict__ dyn, uint32_t own_begin, uint32_t n, uint32_t pad) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t i;
+    if (t < pad) {
+        if (t < pad - dyn->hb) return;  // the window is right-aligned: only its last hb entries are halo particles
+        i = own_begin - pad + t;
+    } else if (t < 2u * pad) {
+        if (t - pad >= dyn->ha) return;
+        i = own_begin + n + (t - pad);
+    } else return;
+    keys_ext[i] = cell_key(p, __ldg(pred_s + i));
+}
+// an empty extended range still needs a valid (all-empty) table
+__global__ void k_slab_fill_if_empty(uint32_t* __restrict__ cell_lb, uint32_t first, uint32_t count, const SlabDyn* __restrict__ dyn) {
+    if (dyn->ext_end != dyn->ext_begin) return;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) cell_lb[first + i] = dyn->ext_begin;
+}
+
 // cell tables over the extended range. start_indices holds GLOBAL sorted indices for owned cells
 // (compute.wgsl:45-56: global particle 0 writes nothing); cell_lb holds local (extended) indices.
 __global__ void __launch_bounds__(GATHER_THREADS)
 k_slab_build_cells(const DevParams p, const uint32_t* __restrict__ keys_ext, uint32_t* __restrict__ start_indices,
                    uint32_t* __restrict__ cell_lb, uint32_t* __restrict__ quirk, uint32_t quirk_c0, uint32_t quirk_stale,
-                   uint32_t fill_lo, uint32_t fill_hi) {
+                   uint32_t fill_lo, uint32_t fill_hi, const SlabDyn* __restrict__ dyn, uint32_t grid_first) {
     // [fill_lo, fill_hi): the table entries the neighbour passes of this band can read (rows row_first-1 .. row_end+1);
     // gaps outside it (half the grid for an edge particle of a 2-rank split) are not filled
-    const uint32_t i = p.ext_begin + blockIdx.x * GATHER_THREADS + threadIdx.x;
-    const bool valid = i < p.ext_end;
+    // dyn == nullptr: the extended range and the global offset are in `p` (host-resolved protocol) and the grid starts
+    // at ext_begin; dyn != nullptr: they were resolved on the device (k_slab_resolve) and the grid covers
+    // [grid_first, ...) = the owned range plus a full pad on both sides
+    const uint32_t ext_begin = dyn ? dyn->ext_begin : p.ext_begin, ext_end = dyn ? dyn->ext_end : p.ext_end;
+    const uint32_t global_offset = dyn ? dyn->global_offset : p.global_offset;
+    const uint32_t i = (dyn ? grid_first : ext_begin) + blockIdx.x * GATHER_THREADS + threadIdx.x;
+    const bool valid = i >= ext_begin && i < ext_end;
     uint32_t gap_begin = 0, gap_end = 0, gap_value = 0;
-    if (blockIdx.x == 0 && threadIdx.x == 0) { quirk[0] = quirk_c0; quirk[1] = quirk_stale; }
+    if (!dyn && blockIdx.x == 0 && threadIdx.x == 0) { quirk[0] = quirk_c0; quirk[1] = quirk_stale; }
     if (valid) {
         const uint32_t kc = min(__ldg(keys_ext + i), p.num_cells - 1u);
         const bool owned = i >= p.own_begin && i < p.own_begin + p.n;
-        const uint32_t gidx = i - p.own_begin + p.global_offset;
-        if (i == p.ext_begin) {
-            gap_begin = 0; gap_end = kc + 1u; gap_value = p.ext_begin;
+        const uint32_t gidx = i - p.own_begin + global_offset;
+        if (i == ext_begin) {
+            gap_begin = 0; gap_end = kc + 1u; gap_value = ext_begin;
             if (owned && gidx > 0u) start_indices[kc] = gidx;  // previous global particle lives on a lower rank, in another row
         } else {
             const uint32_t kp = min(__ldg(keys_ext + i - 1), p.num_cells - 1u);
@@ -127,12 +189,12 @@ k_slab_build_cells(const DevParams p, const uint32_t* __restrict__ keys_ext, uin
     if (gap_end < gap_begin) gap_end = gap_begin;
     warp_fill_gaps(cell_lb, gap_begin, gap_end, gap_value);
     uint32_t tb = 0, te = 0;
-    if (valid && i == p.ext_end - 1u) {
+    if (valid && i == ext_end - 1u) {
         tb = max(min(__ldg(keys_ext + i), p.num_cells - 1u) + 1u, fill_lo);
         te = min(p.num_cells + 1u, fill_hi);
         if (te < tb) te = tb;
     }
-    if (__any_sync(0xffffffffu, te > tb)) warp_fill_gaps(cell_lb, tb, te, p.ext_end);
+    if (__any_sync(0xffffffffu, te > tb)) warp_fill_gaps(cell_lb, tb, te, ext_end);
 }
 // an empty extended range still needs a valid (all-empty) table
 __global__ void k_slab_fill_table(uint32_t* __restrict__ cell_lb, uint32_t first, uint32_t count, uint32_t value) {

@@ -524,6 +524,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
                   const float2* __restrict__ vel_s, const float* __restrict__ rho, const uint32_t* __restrict__ keys,
                   const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk,
                   const float2* __restrict__ force_field, const uint32_t* __restrict__ frame_time,
+                  const uint32_t* __restrict__ global_offset_dev /* slab mode with device-resolved metadata, else null */,
                   float2* __restrict__ pos_out, float2* __restrict__ vel_out, float2* __restrict__ dbg_accel,
                   float2* __restrict__ dbg_abs) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP];
@@ -558,7 +559,8 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     }
     const uint32_t ft = __ldg(frame_time);
     const uint32_t out_i = i - p.own_begin;                      // index in the (halo-free) state arrays
-    uint32_t rand_seed = (out_i + p.global_offset) * 12u + ft * 69u;  // compute.wgsl:161 (global sorted index)
+    const uint32_t goff = p.global_offset + (global_offset_dev ? __ldg(global_offset_dev) : 0u);
+    uint32_t rand_seed = (out_i + goff) * 12u + ft * 69u;  // compute.wgsl:161 (global sorted index)
     const float pressure = fmul(p.pressure_constant, fsub(dens, p.rest_density));
     ForceAcc acc = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     __syncthreads();

@@ -59,6 +59,8 @@ struct Sim {
     uint32_t emig_cap = 0;
     uint32_t* slab_meta = nullptr;
     DevParams slab_params{};
+    uint32_t* slab_dyn = nullptr;             // SlabDyn (kernels_slab.cuh), device-resolved protocol
+    const uint32_t* slab_goff_dev = nullptr;  // &slab_dyn->global_offset while that protocol is in use, else null
 
     uint32_t *jfa_a = nullptr, *jfa_b = nullptr;  // packed seed ping-pong for fluid_sim_jfa_from_particles
     size_t jfa_pixels = 0;

@@ -56,6 +56,8 @@ int fluid_slab_configure(FluidSim* h, int rank, int world, const uint32_t* row_b
     FLUID_CUDA(cudaMalloc(&s->emig_list, (size_t)emig_cap * 8));
     FLUID_CUDA(cudaMalloc(&s->slab_meta, 256));
     FLUID_CUDA(cudaMemsetAsync(s->slab_meta, 0, 256, s->stream));
+    if (!s->slab_dyn) FLUID_CUDA(cudaMalloc(&s->slab_dyn, 64));
+    FLUID_CUDA(cudaMemsetAsync(s->slab_dyn, 0, 64, s->stream));
     s->emig_count = s->slab_meta + 8;  // meta words 0..4, emigrant counter at word 8, per-destination counters at words 16..31
     s->emig_cap = emig_cap;
     s->slab = true;
@@ -90,6 +92,7 @@ int fluid_slab_view(FluidSim* h, FluidSlabView* out) {
     out->pos_sorted = s->pos_s; out->pred_sorted = s->pred_s; out->vel_sorted = s->vel_s; out->rho = s->rho;
     out->keys_ext = s->keys_ext; out->emig_list = s->emig_list; out->emig_count = s->emig_count; out->meta = s->slab_meta;
     out->start_indices = s->start_indices;
+    out->dyn = s->slab_dyn;
     return FLUID_OK;
 }
 
@@ -216,6 +219,7 @@ int fluid_slab_cells_density(FluidSim* h, uint32_t halo_below, uint32_t halo_abo
     p.ext_begin = s->sorted_off - halo_below;
     p.ext_end = s->sorted_off + s->n + halo_above;
     p.global_offset = global_offset;
+    s->slab_goff_dev = nullptr;
     const uint32_t halos = halo_below + halo_above;
     if (halos) {
         k_slab_halo_keys<<<(halos + 255) / 256, 256, 0, s->stream>>>(p, s->pred_s, s->keys_ext, p.ext_begin, halo_below,
@@ -229,11 +233,45 @@ int fluid_slab_cells_density(FluidSim* h, uint32_t halo_below, uint32_t halo_abo
     const uint32_t fill_hi = (uint32_t)std::min<uint64_t>((uint64_t)(brow1 + 1u) * s->grid_w + 1u, (uint64_t)s->num_cells + 1u);
     if (ext) {
         k_slab_build_cells<<<(ext + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
-            p, s->keys_ext, s->start_indices, s->cell_lb, s->quirk, quirk_c0, quirk_stale_ext, fill_lo, fill_hi);
+            p, s->keys_ext, s->start_indices, s->cell_lb, s->quirk, quirk_c0, quirk_stale_ext, fill_lo, fill_hi, nullptr, 0u);
     } else if (fill_hi > fill_lo) {
         k_slab_fill_table<<<(fill_hi - fill_lo + 255) / 256, 256, 0, s->stream>>>(s->cell_lb, fill_lo, fill_hi - fill_lo, p.ext_begin);
     }
     s->launches++;
+    s->mark("cells");
+    if (s->n) {
+        k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho);
+        s->launches++;
+    }
+    s->mark("density");
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+
+// phases 6+7a with the band metadata of every rank still on the device (the all_gather output): no host read between
+// the sort and the force pass. allmeta_dev: world x 8 words (n, first-row count, last-row count, first key, its table
+// entry, 3 unused). Halo rows were received as fixed pad-sized windows: below right-aligned at the owned range,
+// above starting right after it. Errors (a halo row larger than the pad) are latched in the handle and returned by
+// fluid_slab_error_flags on the next host read.
+int fluid_slab_cells_density_dev(FluidSim* h, const uint32_t* allmeta_dev) {
+    SLAB_OR_FAIL(h);
+    if (!allmeta_dev) { set_error("fluid_slab_cells_density_dev: null metadata"); return FLUID_ERR_INVALID_ARGUMENT; }
+    DevParams& p = s->slab_params;
+    p.ext_begin = 0; p.ext_end = 0; p.global_offset = 0;  // resolved on the device
+    SlabDyn* dyn = reinterpret_cast<SlabDyn*>(s->slab_dyn);
+    s->slab_goff_dev = &dyn->global_offset;
+    const uint32_t pad = s->slab_pad;
+    k_slab_resolve<<<1, 32, 0, s->stream>>>(allmeta_dev, s->slab_rows.world, s->slab_rows.rank, s->sorted_off, s->n, pad, dyn, s->quirk);
+    k_slab_halo_keys_dev<<<(2u * pad + 255) / 256, 256, 0, s->stream>>>(p, s->pred_s, s->keys_ext, dyn, s->sorted_off, s->n, pad);
+    const uint32_t brow0 = s->slab_rows.bounds[s->slab_rows.rank], brow1 = s->slab_rows.bounds[s->slab_rows.rank + 1];
+    const uint32_t fill_lo = (brow0 > 0 ? brow0 - 1u : 0u) * s->grid_w;
+    const uint32_t fill_hi = (uint32_t)std::min<uint64_t>((uint64_t)(brow1 + 1u) * s->grid_w + 1u, (uint64_t)s->num_cells + 1u);
+    if (fill_hi > fill_lo)
+        k_slab_fill_if_empty<<<(fill_hi - fill_lo + 255) / 256, 256, 0, s->stream>>>(s->cell_lb, fill_lo, fill_hi - fill_lo, dyn);
+    const uint32_t span = s->n + 2u * pad;
+    k_slab_build_cells<<<(span + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
+        p, s->keys_ext, s->start_indices, s->cell_lb, s->quirk, 0u, 0u, fill_lo, fill_hi, dyn, s->sorted_off - pad);
+    s->launches += 4;
     s->mark("cells");
     if (s->n) {
         k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho);

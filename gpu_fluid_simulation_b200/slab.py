@@ -81,6 +81,7 @@ class SlabRank:
         self.emig_list = _view(v.emig_list, (self.emig_cap,), "<i8", dv)
         self.meta = _view(v.meta, (64,), "<i4", dv)  # words 0..4 band metadata, word 8 emigrant counter, 16.. per destination
         self.dest_counts = self.meta[16:16 + world]
+        self.dyn = _view(v.dyn, (8,), "<i4", dv)  # device-resolved halo counts / offsets / error bits (SlabDyn)
         self.stream = torch.cuda.ExternalStream(self.sim.stream, device=dv)
         self.n = 0
         self.n_emig = 0
@@ -181,6 +182,42 @@ class SlabRank:
         P, n = self.pad, self.n
         return self.rho[P - self.halo_below:P], self.rho[P + n:P + n + self.halo_above]
 
+    # ---- device-resolved protocol: no host read between the sort and the force pass ---------------------------------
+    def meta_raw(self) -> torch.Tensor:
+        """int32[8] view of this rank's band metadata on the device (n, first-row count, last-row count, first key, entry)."""
+        return self.meta[:8]
+
+    def halo_windows(self):
+        """fixed pad-sized windows for the halo exchange of (pred, vel): (to_below, to_above, from_below, from_above),
+        each a list [pred, vel]. My first `pad` owned particles go below (their first row is my first row), my last
+        `pad` go above; the neighbour's window lands right-aligned before / directly after my owned range. Only the
+        halo-row part of a window is ever read (counts are resolved on the device)."""
+        P, n, pad = self.pad, self.n, self.pad
+        out_lo, out_hi = slice(P, P + pad), slice(P + n - pad, P + n)
+        in_lo, in_hi = slice(P - pad, P), slice(P + n, P + n + pad)
+        return ([self.pred_sorted[out_lo], self.vel_sorted[out_lo]], [self.pred_sorted[out_hi], self.vel_sorted[out_hi]],
+                [self.pred_sorted[in_lo], self.vel_sorted[in_lo]], [self.pred_sorted[in_hi], self.vel_sorted[in_hi]])
+
+    def rho_windows(self):
+        P, n, pad = self.pad, self.n, self.pad
+        return (self.rho[P:P + pad], self.rho[P + n - pad:P + n], self.rho[P - pad:P], self.rho[P + n:P + n + pad])
+
+    def cells_density_dev(self, allmeta: torch.Tensor):
+        """allmeta: int32[world * 8] on the device (all_gather of meta_raw)."""
+        self._allmeta_keepalive = allmeta
+        _lib.check(self.lib.fluid_slab_cells_density_dev(self.h, _lib.ptr(allmeta)))
+
+    def error_row(self) -> torch.Tensor:
+        """int64[world] on the device: element 0 = latched error bits of the device-resolved protocol."""
+        with torch.cuda.stream(self.stream):
+            row = torch.zeros(self.world, dtype=torch.int64, device=self.device)
+            row[0:1] = self.dyn[7:8].to(torch.int64)
+            return row
+
+    def raise_on_error_bits(self, bits: int):
+        if bits & 1:
+            raise _lib.FluidError(f"rank {self.rank}: a halo row is larger than the pad {self.pad} (previous tick)")
+
     # ---- phases 6+7 ---------------------------------------------------------------------------------------------------
     def cells_density(self, global_offset, quirk_c0, quirk_stale_global):
         """quirk_*: lowest occupied cell of the whole domain and its stale start_indices entry (a GLOBAL sorted index)."""
@@ -274,11 +311,13 @@ class LocalDriver:
 class DistDriver:
     """one SlabRank per process; exchanges over torch.distributed (NCCL on GPUs, gloo in CPU tests of the protocol)."""
 
-    def __init__(self, rank_obj, group=None):
+    def __init__(self, rank_obj, group=None, device_resolved=None):
         import torch.distributed as dist
         self.dist = dist
         self.r = rank_obj
         self.group = group
+        # device-resolved protocol (one host read per tick instead of two) when the rank object supports it
+        self.device_resolved = hasattr(rank_obj, "cells_density_dev") if device_resolved is None else bool(device_resolved)
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.exchange_bytes = 0
@@ -307,8 +346,11 @@ class DistDriver:
             rc = torch.empty_like(sc)
             self._section("send_counts")
             dist.all_to_all_single(rc, sc, group=self.group)
-            both = torch.stack([sc, rc]).cpu().numpy()  # synchronises
+            rows = [sc, rc] + ([r.error_row()] if self.device_resolved else [])
+            both = torch.stack(rows).cpu().numpy()  # synchronises: the only host read of a device-resolved tick
             send_counts, recv_counts = both[0], both[1]
+            if self.device_resolved:
+                r.raise_on_error_bits(int(both[2][0]))
             self._section("a2a_counts+host")
             payload = r.pack(send_counts)
             self._section("pack")
@@ -321,6 +363,9 @@ class DistDriver:
             self._section("unpack")
             r.sort()
             self._section("sort")
+            if self.device_resolved:
+                self._tick_tail_device_resolved(send_counts, recv_counts)
+                return
             # ---- band metadata of every rank ----
             m = r.meta_tensor()
             allm = torch.empty(W * m.numel(), dtype=m.dtype, device=r.device)
@@ -368,6 +413,50 @@ class DistDriver:
             self._section("force")
         self.last_metas = metas
         self.exchange_bytes = int(16 * (send_counts.sum() + recv_counts.sum()) + 20 * (r.halo_below + r.halo_above + r._first + r._last))
+
+
+def _p2p(dist, group, me, W, to_below, to_above, from_below, from_above):
+    """one batched exchange with both neighbours; every argument is a list of tensors (or a tensor)."""
+    as_list = lambda x: list(x) if isinstance(x, (list, tuple)) else [x]  # noqa: E731
+    ops = []
+    for k in range(len(as_list(to_below))):
+        if me > 0:
+            ops.append(dist.P2POp(dist.isend, as_list(to_below)[k], me - 1, group=group))
+        if me + 1 < W:
+            ops.append(dist.P2POp(dist.isend, as_list(to_above)[k], me + 1, group=group))
+        if me > 0:
+            ops.append(dist.P2POp(dist.irecv, as_list(from_below)[k], me - 1, group=group))
+        if me + 1 < W:
+            ops.append(dist.P2POp(dist.irecv, as_list(from_above)[k], me + 1, group=group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+
+
+def _tick_tail_device_resolved(self, send_counts, recv_counts):
+    """after the sort: metadata all_gather (stays on the device), fixed-size halo windows, cells + density, rho windows,
+    force. Nothing here reads from the device."""
+    dist, r, W, me = self.dist, self.r, self.world, self.rank
+    m = r.meta_raw()
+    allm = torch.empty(W * m.numel(), dtype=m.dtype, device=r.device)
+    dist.all_gather_into_tensor(allm, m, group=self.group)
+    self._section("metas")
+    to_below, to_above, from_below, from_above = r.halo_windows()
+    _p2p(dist, self.group, me, W, to_below, to_above, from_below, from_above)
+    self._section("halo_exchange")
+    r.cells_density_dev(allm)
+    self._section("cells_density")
+    ro_b, ro_a, ri_b, ri_a = r.rho_windows()
+    _p2p(dist, self.group, me, W, ro_b, ro_a, ri_b, ri_a)
+    self._section("rho_exchange")
+    r.force()
+    self._section("force")
+    self.last_metas = None
+    pad = r.pad
+    self.exchange_bytes = int(16 * (send_counts.sum() + recv_counts.sum()) + 20 * pad * ((me > 0) + (me + 1 < W)) * 2)
+
+
+DistDriver._tick_tail_device_resolved = _tick_tail_device_resolved
 
 
 def split_particles(particles: np.ndarray, settings: SimulationSettings, bounds):

@@ -228,6 +228,7 @@ typedef struct FluidSlabView {
     void* emig_count;      /* uint32; emig_count[8 + r] = emigrants bound for rank r */
     void* meta;            /* uint32[5]: n owned, first-row count, last-row count, key of first owned, its start_indices entry */
     void* start_indices;   /* uint32[grid_w*grid_h], global sorted indices for the cells this rank owns */
+    void* dyn;             /* uint32[8]: hb, ha, ext_begin, ext_end, global_offset, quirk c0, quirk stale, error bits */
 } FluidSlabView;
 int fluid_slab_configure(FluidSim* sim, int rank, int world, const uint32_t* row_bounds /* world+1 */, uint32_t capacity,
                          uint32_t pad, uint32_t emig_cap);
@@ -245,6 +246,11 @@ int fluid_slab_sort(FluidSim* sim, uint32_t n_from_below, uint32_t n_from_above,
  * start_indices entry translated to this rank's key-ordered index space (0xffffffff, 0 when not visible) */
 int fluid_slab_cells_density(FluidSim* sim, uint32_t halo_below, uint32_t halo_above, uint32_t global_offset,
                              uint32_t quirk_c0, uint32_t quirk_stale_ext);
+/* phases 6+7a without a host read: allmeta_dev = DEVICE pointer to world x 8 uint32 (every rank's `meta` words, as
+ * gathered by the exchange layer). Halo rows must have been received as pad-sized windows (below: right-aligned at
+ * the owned range; above: starting right after it); halo counts, global offset and the quirk are resolved on the
+ * device. FluidSlabView.dyn[7] latches error bits (1: a halo row exceeds the pad). */
+int fluid_slab_cells_density_dev(FluidSim* sim, const uint32_t* allmeta_dev);
 /* phase 7b: force + integrate of the owned particles */
 int fluid_slab_force(FluidSim* sim);
 

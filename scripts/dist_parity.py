@@ -13,11 +13,14 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ok = True
-for name, (s, ts, p), ticks in (("U400", scenes.uniform_box(400), 12), ("D200x800", scenes.dam_break(200, 800), 25)):
+cases = [(n, sc, t, res) for (n, sc, t) in (("U400", scenes.uniform_box(400), 12), ("D200x800", scenes.dam_break(200, 800), 25))
+         for res in (True, False)]
+for name, (s, ts, p), ticks, resolved in cases:
+    name = f"{name}/{'device' if resolved else 'host'}-resolved"
     r = slab.SlabRank(local, s, rank, world, capacity=p.shape[0], pad=1 << 14)
     bands = slab.split_particles(p, s, r.bounds)
     r.upload_band(bands[rank])
-    drv = slab.DistDriver(r)
+    drv = slab.DistDriver(r, device_resolved=resolved)
     for _ in range(ticks):
         drv.tick(ts)
     r.sync()

@@ -168,12 +168,73 @@ class CpuSlabRank:
 
     def force(self):
         hb, n = self.halo_below, self.n
+        if getattr(self, "_rwi", None) is not None:  # device-resolved protocol: rho arrived in fixed windows
+            self._rho_i = [self._rwi[0][self.pad - hb:].copy(), self._rwi[1][:self.halo_above].copy()]
+            self._rwi = None
         self.ext["density"][:hb] = self._rho_i[0]
         self.ext["density"][hb + n:] = self._rho_i[1]
         u = self._uniform(self.ext.shape[0])
         out = O.move_particle_range(u, self.ext, self.local_table, self.texture, hb, hb + n, self.global_offset - hb)
         self.p = out[hb:hb + n].copy()
         self._first_saved = self._first
+
+    # ---- device-resolved protocol (fixed-size windows, metadata consumed without a driver-side read) ----------------
+    pad = 4096
+
+    def meta_raw(self):
+        m = self.meta_tensor().numpy()
+        out = np.zeros(8, dtype=np.int64)
+        out[:5] = m
+        return torch.from_numpy(out.astype(np.uint32).view(np.int32).copy())
+
+    @staticmethod
+    def _window(arr, pad, right_aligned):
+        """first / last `pad` rows of arr as a fixed-size window (zero filled where the band is shorter)."""
+        w = np.zeros((pad,) + arr.shape[1:], dtype=arr.dtype)
+        k = min(pad, arr.shape[0])
+        if right_aligned:
+            w[pad - k:] = arr[arr.shape[0] - k:]
+        else:
+            w[:k] = arr[:k]
+        return w
+
+    def halo_windows(self):
+        pad = self.pad
+        self._wout = [self._window(self.p[k], pad, False) for k in ("predicted_position", "velocity")] + \
+                     [self._window(self.p[k], pad, True) for k in ("predicted_position", "velocity")]
+        self._win = [np.zeros((pad, 2), np.float32) for _ in range(4)]
+        t, u = [torch.from_numpy(a) for a in self._wout], [torch.from_numpy(a) for a in self._win]
+        return [t[0], t[1]], [t[2], t[3]], [u[0], u[1]], [u[2], u[3]]
+
+    def cells_density_dev(self, allmeta):
+        m = allmeta.numpy().view(np.uint32).reshape(self.world, 8).astype(np.int64)
+        me = self.rank
+        hb = int(m[me - 1, 2]) if me > 0 else 0
+        ha = int(m[me + 1, 1]) if me + 1 < self.world else 0
+        assert hb <= self.pad and ha <= self.pad
+        prefix = int(m[:me, 0].sum())
+        c0, stale = NO_QUIRK, 0
+        for r in range(self.world):
+            if m[r, 0] > 0:
+                c0, stale = int(m[r, 3]), int(m[r, 4])
+                break
+        self.halo_below, self.halo_above = hb, ha
+        pad = self.pad
+        self._in = [self._win[0][pad - hb:], self._win[1][pad - hb:], self._win[2][:ha], self._win[3][:ha]]
+        self.cells_density(prefix, c0, stale)
+
+    def rho_windows(self):
+        pad = self.pad
+        self._rwo = [self._window(self.p["density"], pad, False), self._window(self.p["density"], pad, True)]
+        self._rwi = [np.zeros(pad, np.float32), np.zeros(pad, np.float32)]
+        return (torch.from_numpy(self._rwo[0]), torch.from_numpy(self._rwo[1]), torch.from_numpy(self._rwi[0]),
+                torch.from_numpy(self._rwi[1]))
+
+    def error_row(self):
+        return torch.zeros(self.world, dtype=torch.int64)
+
+    def raise_on_error_bits(self, bits):
+        assert bits == 0
 
     def close(self):
         pass

@@ -42,7 +42,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, scene, ticks):
+def _worker(rank, world, port, scene, ticks, resolved):
     import sys
     sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
     import torch.distributed as dist
@@ -72,7 +72,7 @@ def _worker(rank, world, port, scene, ticks):
         r = CpuSlabRank(s, rank, world)
         bands = slab.split_particles(p, s, r.bounds)
         r.upload_band(bands[rank])
-        drv = slab.DistDriver(r)
+        drv = slab.DistDriver(r, device_resolved=resolved)
         for _ in range(ticks):
             drv.tick(ts)
         lo, hi = r.owns_rows()
@@ -97,6 +97,9 @@ def _worker(rank, world, port, scene, ticks):
         dist.destroy_process_group()
 
 
+@pytest.mark.parametrize("resolved", [False, True], ids=["host-resolved", "device-resolved"])
 @pytest.mark.parametrize("world,scene,ticks", [(2, "uniform", 4), (3, "dam", 10), (2, "default", 3), (3, "fast", 3)])
-def test_dist_driver_over_gloo_matches_single_domain(oracle, world, scene, ticks):
-    mp.spawn(_worker, args=(world, _free_port(), scene, ticks), nprocs=world, join=True)
+def test_dist_driver_over_gloo_matches_single_domain(oracle, world, scene, ticks, resolved):
+    """both exchange protocols of DistDriver: metadata read back by the host between sort and cells (two host reads per
+    tick), and the device-resolved one (fixed-size halo windows, one host read per tick)."""
+    mp.spawn(_worker, args=(world, _free_port(), scene, ticks, resolved), nprocs=world, join=True)
