@@ -138,7 +138,7 @@ static int field_from_device_mask(Sim* s, uint8_t* mask_out, uint32_t* seeds_out
     k_mask_has_white<<<blocks, 256, 0, s->stream>>>(s->mask_dev, npx, s->mask_flag);
     k_seed_from_mask<<<blocks, 256, 0, s->stream>>>(s->mask_dev, w, h, s->mask_flag, s->jfa_a);
     s->launches += 2;
-    uint32_t* res = jfa_run_device(s->jfa_a, s->jfa_b, w, h, s->stream, &s->launches, true);
+    uint32_t* res = jfa_run_device(s->jfa_a, s->jfa_b, w, h, s->stream, &s->launches, false, h <= w + 1u);
     k_to_force_field<<<blocks, 256, 0, s->stream>>>(res, w, h, s->force_field);
     s->launches++;
     if (ms_out) cudaEventRecord(e1, s->stream);

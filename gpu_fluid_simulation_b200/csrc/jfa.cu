@@ -35,6 +35,18 @@ __device__ __forceinline__ void consider(uint32_t n, int x, int y, uint32_t widt
     if (d < best_d) { best = n; best_d = d; }
 }
 
+// Canonical seed images: every value is either JFA_INVALID_PACKED or a seed the shader would never skip
+// (sx <= width and sy <= width). Then the skip test of jump_flood.wgsl:48 can be dropped: an INVALID neighbour acts
+// as a phantom seed at (32767, 32767), whose distance from any pixel (x, y <= 16383) exceeds the distance to every
+// admissible seed (|x - sx| <= 16384 <= 32767 - x, never with equality on both axes) and ties with an INVALID
+// incumbent (same phantom point, strict <) — so it never replaces anything, exactly like the skip. Everything the
+// library generates itself (mask / particle seeds on images with h <= w + 1) is canonical; caller-supplied seed
+// images are checked while they are packed and fall back to the general kernels otherwise.
+__device__ __forceinline__ void consider_fast(uint32_t n, int x, int y, uint32_t& best, int& best_d) {
+    const int d = sq_dist(x, y, (int)(n & 0xffffu), (int)(n >> 16));
+    if (d < best_d) { best = n; best_d = d; }
+}
+
 // ---- generic pass: any jump, 1 pixel per thread ------------------------------------------------
 __global__ void __launch_bounds__(256) k_jfa_pass_scalar(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
                                                          uint32_t w, uint32_t h, int j) {
@@ -55,6 +67,7 @@ __global__ void __launch_bounds__(256) k_jfa_pass_scalar(const uint32_t* __restr
 }
 
 // ---- vector pass: w % 4 == 0 and j % 4 == 0; 4 pixels per thread, uint4 loads -------------------
+template <bool CANON>
 __global__ void __launch_bounds__(256) k_jfa_pass_vec4(const uint4* __restrict__ in, uint4* __restrict__ out,
                                                        uint32_t w, uint32_t h, int j) {
     const uint32_t w4 = w >> 2;
@@ -73,10 +86,54 @@ __global__ void __launch_bounds__(256) k_jfa_pass_vec4(const uint4* __restrict__
         const int nx4 = (int)x4 + (kk % 3 - 1) * j4, ny = yi + (kk / 3 - 1) * j;
         if (nx4 < 0 || ny < 0 || nx4 >= (int)w4 || ny >= (int)h) continue;  // whole 4-group in or out (w, j multiples of 4)
         const uint4 nb = __ldg(in + (size_t)ny * w4 + (size_t)nx4);
-        consider(nb.x, x0 + 0, yi, w, best[0], best_d[0]);
-        consider(nb.y, x0 + 1, yi, w, best[1], best_d[1]);
-        consider(nb.z, x0 + 2, yi, w, best[2], best_d[2]);
-        consider(nb.w, x0 + 3, yi, w, best[3], best_d[3]);
+        if (CANON) {
+            consider_fast(nb.x, x0 + 0, yi, best[0], best_d[0]);
+            consider_fast(nb.y, x0 + 1, yi, best[1], best_d[1]);
+            consider_fast(nb.z, x0 + 2, yi, best[2], best_d[2]);
+            consider_fast(nb.w, x0 + 3, yi, best[3], best_d[3]);
+        } else {
+            consider(nb.x, x0 + 0, yi, w, best[0], best_d[0]);
+            consider(nb.y, x0 + 1, yi, w, best[1], best_d[1]);
+            consider(nb.z, x0 + 2, yi, w, best[2], best_d[2]);
+            consider(nb.w, x0 + 3, yi, w, best[3], best_d[3]);
+        }
+    }
+    out[(size_t)y * w4 + x4] = make_uint4(best[0], best[1], best[2], best[3]);
+}
+
+// ---- window pass: jumps 1 and 2 (not multiples of 4) on canonical images with w % 4 == 0 -----------------------
+// 4 pixels per thread like the vector pass; per neighbour row the three aligned uint4 around the thread's own group
+// form a 12-pixel window and the neighbours at x -+ J are picked from it with compile-time indices. Groups outside
+// the image are replaced by INVALID, which never wins on a canonical image (= the shader's out-of-image skip).
+template <int J>
+__global__ void __launch_bounds__(256) k_jfa_pass_win(const uint4* __restrict__ in, uint4* __restrict__ out,
+                                                      uint32_t w, uint32_t h) {
+    const uint32_t w4 = w >> 2;
+    const uint32_t x4 = blockIdx.x * 64u + (threadIdx.x & 63u);
+    const uint32_t y = blockIdx.y * 4u + (threadIdx.x >> 6);
+    if (x4 >= w4 || y >= h) return;
+    const int yi = (int)y, x0 = (int)(x4 << 2);
+    const uint4 inv4 = make_uint4(JFA_INVALID_PACKED, JFA_INVALID_PACKED, JFA_INVALID_PACKED, JFA_INVALID_PACKED);
+    const uint4 own = __ldg(in + (size_t)y * w4 + x4);
+    uint32_t best[4] = {own.x, own.y, own.z, own.w};
+    int best_d[4];
+#pragma unroll
+    for (int c = 0; c < 4; c++) best_d[c] = sq_dist(x0 + c, yi, (int)(best[c] & 0xffffu), (int)(best[c] >> 16));
+#pragma unroll
+    for (int r = -1; r <= 1; r++) {  // rows y-J, y, y+J; inside a row: x-J, x (not for the own row), x+J (jump_flood.wgsl:38-46)
+        const int ny = yi + r * J;
+        if (ny < 0 || ny >= (int)h) continue;
+        const uint4* row = in + (size_t)ny * w4;
+        const uint4 lq = x4 > 0u ? __ldg(row + x4 - 1u) : inv4;
+        const uint4 cq = r == 0 ? own : __ldg(row + x4);
+        const uint4 rq = x4 + 1u < w4 ? __ldg(row + x4 + 1u) : inv4;
+        const uint32_t win[12] = {lq.x, lq.y, lq.z, lq.w, cq.x, cq.y, cq.z, cq.w, rq.x, rq.y, rq.z, rq.w};
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            consider_fast(win[4 + c - J], x0 + c, yi, best[c], best_d[c]);
+            if (r != 0) consider_fast(win[4 + c], x0 + c, yi, best[c], best_d[c]);
+            consider_fast(win[4 + c + J], x0 + c, yi, best[c], best_d[c]);
+        }
     }
     out[(size_t)y * w4 + x4] = make_uint4(best[0], best[1], best[2], best[3]);
 }
@@ -139,13 +196,17 @@ __global__ void __launch_bounds__(256) k_jfa_tail(const uint32_t* __restrict__ i
 }
 
 // ---- boundary conversions -----------------------------------------------------------------------
-__global__ void k_pack_rg32(const uint2* __restrict__ rg, uint32_t* __restrict__ packed, size_t npx) {
+// noncanon (optional): set to 1 if some value is neither INVALID nor a seed the shader never skips (see consider_fast)
+__global__ void k_pack_rg32(const uint2* __restrict__ rg, uint32_t* __restrict__ packed, size_t npx, uint32_t width,
+                            uint32_t* __restrict__ noncanon) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= npx) return;
     uint2 v = __ldg(rg + i);
     // coordinates above 65535 cannot be packed; they can only be "invalid" markers (> width), keep them invalid
     uint32_t x = v.x > 0xffffu ? 0xffffu : v.x, y = v.y > 0xffffu ? 0xffffu : v.y;
-    packed[i] = x | (y << 16);
+    const uint32_t pk = x | (y << 16);
+    packed[i] = pk;
+    if (noncanon && pk != JFA_INVALID_PACKED && (x > width || y > width)) *noncanon = 1u;
 }
 __global__ void k_unpack_rg32(const uint32_t* __restrict__ packed, uint2* __restrict__ rg, size_t npx) {
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -221,10 +282,16 @@ static uint32_t first_jump(uint32_t w, uint32_t h) {  // 2^(ceil(log2 max(w,h)) 
     return l == 0 ? 0u : (1u << (l - 1));
 }
 
-static void launch_pass(const uint32_t* in, uint32_t* out, uint32_t w, uint32_t h, uint32_t j, cudaStream_t st) {
-    if ((w & 3u) == 0 && (j & 3u) == 0) {
+static void launch_pass(const uint32_t* in, uint32_t* out, uint32_t w, uint32_t h, uint32_t j, cudaStream_t st, bool canonical) {
+    const bool vec = (w & 3u) == 0;
+    if (vec && (j & 3u) == 0) {
         dim3 grid(((w >> 2) + 63) / 64, (h + 3) / 4);
-        k_jfa_pass_vec4<<<grid, 256, 0, st>>>(reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), w, h, (int)j);
+        if (canonical) k_jfa_pass_vec4<true><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), w, h, (int)j);
+        else k_jfa_pass_vec4<false><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), w, h, (int)j);
+    } else if (vec && canonical && (j == 1u || j == 2u)) {
+        dim3 grid(((w >> 2) + 63) / 64, (h + 3) / 4);
+        if (j == 1u) k_jfa_pass_win<1><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), w, h);
+        else k_jfa_pass_win<2><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4*>(in), reinterpret_cast<uint4*>(out), w, h);
     } else {
         dim3 grid((w + 63) / 64, (h + 3) / 4);
         k_jfa_pass_scalar<<<grid, 256, 0, st>>>(in, out, w, h, (int)j);
@@ -232,14 +299,19 @@ static void launch_pass(const uint32_t* in, uint32_t* out, uint32_t w, uint32_t 
 }
 
 // runs the whole schedule on packed device buffers a (input) / b (scratch); returns the buffer holding the result.
-// *launches is incremented per kernel.
-uint32_t* jfa_run_device(uint32_t* a, uint32_t* b, uint32_t w, uint32_t h, cudaStream_t st, uint64_t* launches, bool fuse_tail) {
+// *launches is incremented per kernel. canonical: see consider_fast. fuse_tail: run the jumps <= TAIL_JUMP in the
+// shared-memory tile kernel instead of one global pass each — measured SLOWER on B200 (ncu, 4096^2: k_jfa_tail 609 us
+// for 3 jumps at 85 % issue-active against 47-79 us per global pass, whose reads are L2 hits anyway: the passes are
+// instruction bound, ~125 thread instructions per pixel, so tiling buys nothing and its halo costs extra work), so
+// every caller passes false; the kernel stays for images where that balance differs.
+uint32_t* jfa_run_device(uint32_t* a, uint32_t* b, uint32_t w, uint32_t h, cudaStream_t st, uint64_t* launches, bool fuse_tail,
+                         bool canonical) {
     uint32_t* src = a;
     uint32_t* dst = b;
     static bool attr_set = false;
     constexpr int H = 2 * TAIL_JUMP - 1;
     constexpr size_t tail_smem = (size_t)2 * (TAIL_TX + 2 * H) * (TAIL_TY + 2 * H) * 4;
-    if (!attr_set) {
+    if (fuse_tail && !attr_set) {
         cudaFuncSetAttribute(k_jfa_tail<TAIL_JUMP, TAIL_TX, TAIL_TY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tail_smem);
         attr_set = true;
     }
@@ -251,7 +323,7 @@ uint32_t* jfa_run_device(uint32_t* a, uint32_t* b, uint32_t w, uint32_t h, cudaS
             uint32_t* t = src; src = dst; dst = t;
             break;
         }
-        launch_pass(src, dst, w, h, j, st);
+        launch_pass(src, dst, w, h, j, st, canonical);
         if (launches) (*launches)++;
         uint32_t* t = src; src = dst; dst = t;
     }
@@ -299,8 +371,12 @@ int fluid_jfa_run(const uint32_t* seeds_in, uint32_t w, uint32_t h, uint32_t* se
     FLUID_CUDA(cudaMalloc(&s.a, npx * 4)); FLUID_CUDA(cudaMalloc(&s.b, npx * 4)); FLUID_CUDA(cudaMalloc(&s.io, npx * 8));
     FLUID_CUDA(cudaMemcpyAsync(s.io, seeds_in, npx * 8, cudaMemcpyHostToDevice, s.st));
     const unsigned blocks = (unsigned)((npx + 255) / 256);
-    k_pack_rg32<<<blocks, 256, 0, s.st>>>(reinterpret_cast<const uint2*>(s.io), s.a, npx);
-    uint32_t* res = jfa_run_device(s.a, s.b, w, h, s.st, nullptr, true);
+    FLUID_CUDA(cudaMemsetAsync(s.b, 0, 4, s.st));  // s.b doubles as the non-canonical flag before the first pass overwrites it
+    k_pack_rg32<<<blocks, 256, 0, s.st>>>(reinterpret_cast<const uint2*>(s.io), s.a, npx, w, s.b);
+    uint32_t noncanon = 1;
+    FLUID_CUDA(cudaMemcpyAsync(&noncanon, s.b, 4, cudaMemcpyDeviceToHost, s.st));
+    FLUID_CUDA(cudaStreamSynchronize(s.st));
+    uint32_t* res = jfa_run_device(s.a, s.b, w, h, s.st, nullptr, false, noncanon == 0);
     k_unpack_rg32<<<blocks, 256, 0, s.st>>>(res, reinterpret_cast<uint2*>(s.io), npx);
     FLUID_CUDA(cudaMemcpyAsync(seeds_out, s.io, npx * 8, cudaMemcpyDeviceToHost, s.st));
     FLUID_CUDA(cudaStreamSynchronize(s.st));
@@ -318,8 +394,12 @@ int fluid_jfa_pass(const uint32_t* seeds_in, uint32_t w, uint32_t h, uint32_t ju
     FLUID_CUDA(cudaMalloc(&s.a, npx * 4)); FLUID_CUDA(cudaMalloc(&s.b, npx * 4)); FLUID_CUDA(cudaMalloc(&s.io, npx * 8));
     FLUID_CUDA(cudaMemcpyAsync(s.io, seeds_in, npx * 8, cudaMemcpyHostToDevice, s.st));
     const unsigned blocks = (unsigned)((npx + 255) / 256);
-    k_pack_rg32<<<blocks, 256, 0, s.st>>>(reinterpret_cast<const uint2*>(s.io), s.a, npx);
-    launch_pass(s.a, s.b, w, h, jump, s.st);
+    FLUID_CUDA(cudaMemsetAsync(s.b, 0, 4, s.st));
+    k_pack_rg32<<<blocks, 256, 0, s.st>>>(reinterpret_cast<const uint2*>(s.io), s.a, npx, w, s.b);
+    uint32_t noncanon = 1;
+    FLUID_CUDA(cudaMemcpyAsync(&noncanon, s.b, 4, cudaMemcpyDeviceToHost, s.st));
+    FLUID_CUDA(cudaStreamSynchronize(s.st));
+    launch_pass(s.a, s.b, w, h, jump, s.st, noncanon == 0);
     k_unpack_rg32<<<blocks, 256, 0, s.st>>>(s.b, reinterpret_cast<uint2*>(s.io), npx);
     FLUID_CUDA(cudaMemcpyAsync(seeds_out, s.io, npx * 8, cudaMemcpyDeviceToHost, s.st));
     FLUID_CUDA(cudaStreamSynchronize(s.st));
@@ -385,7 +465,7 @@ int fluid_jfa_to_force_field(const uint32_t* seeds, uint32_t w, uint32_t h, floa
     FLUID_CUDA(cudaMalloc(&s.a, npx * 4)); FLUID_CUDA(cudaMalloc(&s.io, npx * 8));
     FLUID_CUDA(cudaMemcpyAsync(s.io, seeds, npx * 8, cudaMemcpyHostToDevice, s.st));
     const unsigned blocks = (unsigned)((npx + 255) / 256);
-    k_pack_rg32<<<blocks, 256, 0, s.st>>>(reinterpret_cast<const uint2*>(s.io), s.a, npx);
+    k_pack_rg32<<<blocks, 256, 0, s.st>>>(reinterpret_cast<const uint2*>(s.io), s.a, npx, w, nullptr);
     k_to_force_field<<<blocks, 256, 0, s.st>>>(s.a, w, h, reinterpret_cast<float2*>(s.io));
     FLUID_CUDA(cudaMemcpyAsync(field_xy, s.io, npx * 8, cudaMemcpyDeviceToHost, s.st));
     FLUID_CUDA(cudaStreamSynchronize(s.st));
@@ -415,7 +495,9 @@ int fluid_sim_jfa_from_particles(FluidSim* h_, uint32_t w, uint32_t h, uint32_t*
     cudaEvent_t e0, e1;
     FLUID_CUDA(cudaEventCreate(&e0)); FLUID_CUDA(cudaEventCreate(&e1));
     cudaEventRecord(e0, s->stream);
-    uint32_t* res = jfa_run_device(s->jfa_a, s->jfa_b, w, h, s->stream, &s->launches, true);
+    // seeds from particles are their own in-image coordinates: canonical unless the shader's `> width` test can reject
+    // a row index (images taller than wide)
+    uint32_t* res = jfa_run_device(s->jfa_a, s->jfa_b, w, h, s->stream, &s->launches, false, h <= w + 1u);
     cudaEventRecord(e1, s->stream);
     void* io = nullptr;
     const bool want_io = seeds_out || field_xy_out;

@@ -80,3 +80,33 @@ def test_config4_jfa_4096_from_particles(fluid, oracle, size, n_side):
             seeds, fld, ms = sim.jfa_from_particles(size, size)
         assert np.array_equal(seeds, ref)
         assert np.array_equal(fld, oracle.jfa_to_force_field(ref))
+
+
+def test_non_canonical_seed_images_take_the_general_path(fluid, oracle):
+    """caller-supplied seed values the shader would skip as neighbours (coordinate > width) but that are not the
+    INVALID marker: the fast kernels' no-skip argument does not hold, the library must detect them while packing and
+    fall back to the general kernels. Also partially-invalid pairs and sx == width (admitted by the shader's `>`)."""
+    rng = np.random.default_rng(11)
+    for h, w in ((64, 64), (96, 128), (128, 96)):
+        seeds = oracle.jfa_seed_from_mask(_random_seeds(rng, h, w, 0.02))
+        odd = rng.random((h, w)) < 0.01
+        seeds[odd, 0] = rng.integers(w + 1, 32768, size=int(odd.sum()))       # x beyond the width (<= 32767: the shader's i32 distance must not overflow)
+        half = rng.random((h, w)) < 0.005
+        seeds[half, 1] = 32767                                                 # only one channel invalid
+        edge = rng.random((h, w)) < 0.005
+        seeds[edge] = (w, min(h - 1, w))                                       # sx == width: not skipped
+        assert np.array_equal(fluid.jfa.jfa_run(seeds), oracle.jfa_run(seeds))
+        for jump in (1, 2, 4, 16):
+            assert np.array_equal(fluid.jfa.jfa_pass(seeds, jump), oracle.jfa_pass(seeds, jump))
+
+
+@pytest.mark.parametrize("h,w", [(512, 512), (257, 256), (255, 256), (100, 4), (8, 8)])
+def test_canonical_fast_path_every_jump(fluid, oracle, h, w):
+    """images the window / no-skip kernels are used for (w % 4 == 0, h <= w + 1), pass by pass incl. jumps 1 and 2 at
+    the image borders, dense and sparse seeds."""
+    rng = np.random.default_rng(h * 7 + w)
+    for frac in (0.3, 0.002):
+        seeds = oracle.jfa_seed_from_mask(_random_seeds(rng, h, w, frac))
+        for jump in (1, 2, 4, 8, 64):
+            assert np.array_equal(fluid.jfa.jfa_pass(seeds, jump), oracle.jfa_pass(seeds, jump)), (jump, frac)
+        assert np.array_equal(fluid.jfa.jfa_run(seeds), oracle.jfa_run(seeds))
