@@ -172,6 +172,10 @@ DevParams Sim::make_params(const FluidSimUniform& u) const {
     p.inv_two_h3 = 1.0f / p.two_h3;
     p.inv_h2 = 1.0f / p.h2;
     p.exact_math = exact_math ? 1 : 0;
+    {
+        const float lo_h = 9.5367431640625e-07f /* 2^-20 */, hi_h = 1048576.0f /* 2^20 */, lo_b = 8.6736174e-19f /* 2^-60 */, hi_b = 6.338253e29f /* 2^99 */;
+        p.key_fast_div = (p.h >= lo_h && p.h <= hi_h && p.half_x >= lo_b && p.half_x <= hi_b && p.half_y >= lo_b && p.half_y <= hi_b) ? 1 : 0;
+    }
     return p;
 }
 

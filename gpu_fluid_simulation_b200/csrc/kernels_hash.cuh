@@ -34,6 +34,7 @@ k_predict_key_hist(const DevParams p, const float2* __restrict__ pos, const floa
     const float4* pos4 = reinterpret_cast<const float4*>(pos);
     const float4* vel4 = reinterpret_cast<const float4*>(vel);
     const uint32_t stride = gridDim.x * HASH_THREADS;
+    const float y_h = rcp_refined(p.h);  // the key's two divisions by h share it (common.cuh: cell_key_shared)
     // loop bound rounded up to a warp multiple so that match_any always sees a full warp
     const uint32_t n_iter_end = (n_pairs + 31u) & ~31u;
     for (uint32_t i = blockIdx.x * HASH_THREADS + threadIdx.x; i < n_iter_end; i += stride) {
@@ -42,8 +43,10 @@ k_predict_key_hist(const DevParams p, const float2* __restrict__ pos, const floa
         uint32_t k0 = 0, k1 = 0;
         if (v0) {
             float4 ps = __ldg(pos4 + i), vs = __ldg(vel4 + i);  // arrays are padded to an even length
-            k0 = cell_key(p, predict_position(p, make_float2(ps.x, ps.y), make_float2(vs.x, vs.y)));
-            k1 = cell_key(p, predict_position(p, make_float2(ps.z, ps.w), make_float2(vs.z, vs.w)));
+            const float2 q0 = predict_position(p, make_float2(ps.x, ps.y), make_float2(vs.x, vs.y));
+            const float2 q1 = predict_position(p, make_float2(ps.z, ps.w), make_float2(vs.z, vs.w));
+            if (p.key_fast_div) { k0 = cell_key_shared(p, q0, y_h); k1 = cell_key_shared(p, q1, y_h); }
+            else { k0 = cell_key(p, q0); k1 = cell_key(p, q1); }
             if (v1) reinterpret_cast<uint2*>(keys)[i] = make_uint2(k0, k1);
             else keys[2u * i] = k0;
         }

@@ -39,11 +39,13 @@ k_slab_key_hist(const DevParams p, const float2* __restrict__ pos, const float2*
     const uint32_t stride = gridDim.x * HASH_THREADS;
     const uint32_t end = (count + 31u) & ~31u;
     const uint32_t row_lo = rows.bounds[rows.rank], row_hi = rows.bounds[rows.rank + 1];
+    const float y_h = rcp_refined(p.h);
     for (uint32_t i = blockIdx.x * HASH_THREADS + threadIdx.x; i < end; i += stride) {
         const bool v = i < count;
         uint32_t k = 0;
         if (v) {
-            k = cell_key(p, predict_position(p, __ldg(pos + i), __ldg(vel + i)));
+            const float2 q = predict_position(p, __ldg(pos + i), __ldg(vel + i));
+            k = p.key_fast_div ? cell_key_shared(p, q, y_h) : cell_key(p, q);
             if (detect_emigrants) {
                 const uint32_t row = k / p.grid_w;
                 if (row < row_lo || row >= row_hi) {
