@@ -98,3 +98,21 @@ def render(sim, inv_proj, w: int = 960, h: int = 540, want_f32=True, want_rgba8=
     _lib.check(sim._lib.fluid_sim_render(sim._h, _lib.ptr(m), int(w), int(h), _lib.ptr(f), _lib.ptr(b),
                                         C.byref(ms) if timed else None))
     return f, b, (ms.value if timed else None)
+
+
+def surface_tension(sim) -> np.ndarray:
+    """row f4: calculate_surface_tension (compute.wgsl:300-498) for every sorted particle of the last tick's state;
+    float32[n, 2]. The reference's call is commented out (compute.wgsl:92), so nothing is applied to the sim."""
+    out = np.empty((sim.particle_count, 2), dtype=np.float32)
+    _lib.check(sim._lib.fluid_sim_surface_tension(sim._h, _lib.ptr(out)))
+    return out
+
+
+def mouse_world_pos(cursor_xy, window_size, inv_proj) -> np.ndarray:
+    """CursorMoved mapping of src/main.rs:287-303: window pixel -> TickSettings.mouse_pos (world space)."""
+    c = np.ascontiguousarray(cursor_xy, dtype=np.float32).reshape(2)
+    w = np.ascontiguousarray(window_size, dtype=np.float32).reshape(2)
+    m = np.ascontiguousarray(inv_proj, dtype=np.float32).reshape(16)
+    out = np.empty(2, dtype=np.float32)
+    _lib.check(_lib.load().fluid_mouse_world_pos(_lib.ptr(c), _lib.ptr(w), _lib.ptr(m), _lib.ptr(out)))
+    return out

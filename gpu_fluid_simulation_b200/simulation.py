@@ -101,6 +101,13 @@ class FluidSimulation:
             self._lib.fluid_sim_destroy(self._h)
             self._h = C.c_void_p()
 
+    def restart(self):
+        """reference: Renderer::restart_simulation (src/renderer.rs:870-872) — a fresh FluidSimulation::new with the
+        same SimulationSettings: spawn grid, zero velocities, tick 0, start table and field re-initialised."""
+        self.close()
+        cs = self.settings.to_c()
+        _lib.check(self._lib.fluid_sim_create(C.byref(cs), self.device, C.byref(self._h)))
+
     def __del__(self):
         try:
             self.close()

@@ -313,6 +313,17 @@ int fluid_sim_field_from_mask(FluidSim* sim, const uint8_t* mask, uint32_t* seed
 int fluid_sim_render(FluidSim* sim, const float inv_proj[16], uint32_t w, uint32_t h, float* rgba_f32_out,
                      uint8_t* rgba8_out, float* ms_out);
 
+/* ---- dormant physics --------------------------------------------------------
+ * calculate_surface_tension (compute.wgsl:300-498; poly6_kernel_gradient / _laplacian funcs.wgsl:81-98) evaluated
+ * for every particle of the sim's CURRENT sorted state (predicted positions, densities, keys and start_indices of
+ * the last tick, treshold / coefficient / mass / frame_time of that tick's uniform). The reference's call is
+ * commented out (compute.wgsl:92), so the result is NOT applied to the particles: force_xy_out (HOST, 2 floats
+ * per particle in sorted order) is a diagnostic, bit-identical to the shader arithmetic's CPU restatement. */
+int fluid_sim_surface_tension(FluidSim* sim, float* force_xy_out);
+/* CursorMoved mapping of src/main.rs:287-303: window pixel -> world position for FluidTickSettings.mouse_pos
+ * (ndc = cursor/window*2-1, clip = (ndc.x, -ndc.y, 0, 1), world = (inv_proj*clip).xy / w). Host arithmetic only. */
+int fluid_mouse_world_pos(const float cursor_xy[2], const float window_size[2], const float inv_proj[16], float world_xy_out[2]);
+
 /* ---- device self-tests ------------------------------------------------------------ */
 /* The exact-math force pass computes the 9 divisions of a neighbour pair (compute.wgsl:206-223, :283-288,
  * funcs.wgsl:112-123) from shared, refined reciprocals. This sweeps every significand of the divisor at 13

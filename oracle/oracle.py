@@ -273,6 +273,13 @@ def render_fluid(u, p, table, inv_proj, w, h):
     return out
 
 
+def surface_tension(u, p, table):
+    """the reference's dormant calculate_surface_tension per particle -> float32[n, 2] (not applied to the state)."""
+    out = np.empty((p.shape[0], 2), dtype=np.float32)
+    lib().oracle_surface_tension(C.byref(u), _p(p), _p(table), _p(out))
+    return out
+
+
 def bruteforce_density_f64(u, p):
     out = np.empty(p.shape[0], dtype=np.float64)
     lib().oracle_bruteforce_density_f64(C.byref(u), _p(p), _p(out))

@@ -133,4 +133,85 @@ void oracle_render_fluid(const FluidSimUniform* u, const FluidParticle* p, const
     }
 }
 
+
+// ---- dormant physics: surface tension (compute.wgsl:300-498; the call at :92 is commented out in the reference) ----
+// per particle: f = calculate_surface_tension(particle.predicted_position), NOT applied to the state (as in the
+// reference). Neighbour walks as in the shader (start_indices entry, stop at the first foreign key; self is not
+// skipped); cells outside the table are empty [pinned]; pow(h, 8) with powf; PI = 3.14159265359 (funcs.wgsl:54).
+// Note: poly6_kernel_gradient is handed the UNIT direction (compute.wgsl:440), so for h <= 1 it returns 0 for every
+// neighbour (r_len = 1 >= h) and the whole term vanishes at the reference's h = 0.2.
+}  // extern "C"
+namespace {
+const float ST_PI = 3.14159265359f;
+inline uint32_t st_xorshift32(uint32_t& s) { uint32_t x = s; x ^= x << 13; x ^= x >> 17; x ^= x << 5; s = x; return x; }
+inline float st_rand_f32(uint32_t& s) { return (float)st_xorshift32(s) / 4294967296.0f; }
+template <class F>
+inline void st_walk(const FluidSimUniform* u, const FluidParticle* p, const uint32_t* start_indices, float px, float py, F&& body) {
+    const uint32_t num_cells = u->grid_w * u->grid_h;
+    const int32_t cellx = (int32_t)(f2u_sat(floorf((px + u->bounds[0] * 0.5f) / u->smoothing_radius)) + 1u);
+    const int32_t celly = (int32_t)(f2u_sat(floorf((py + u->bounds[1] * 0.5f) / u->smoothing_radius)) + 1u);
+    for (int oy = -1; oy <= 1; oy++)
+        for (int ox = -1; ox <= 1; ox++) {
+            const uint32_t x = (uint32_t)(cellx + ox), y = (uint32_t)(celly + oy);
+            const uint32_t id = y * u->grid_w + x;
+            if (id >= num_cells) continue;
+            uint32_t si = start_indices[id];
+            while (si < u->particle_count && p[si].grid == id) { body(p[si]); si++; }
+        }
+}
+}  // namespace
+
+extern "C" {
+void oracle_surface_tension(const FluidSimUniform* u, const FluidParticle* p, const uint32_t* start_indices, float* out_xy) {
+    const float h = u->smoothing_radius;
+    const float h8 = powf(h, 8.0f);
+    const float c_grad = -24.0f / (ST_PI * h8), c_lap = 8.0f / (ST_PI * h8);
+#pragma omp parallel for schedule(dynamic, 256)
+    for (int64_t id = 0; id < (int64_t)u->particle_count; id++) {
+        const float px = p[id].predicted_position[0], py = p[id].predicted_position[1];
+        // calculate_colour_field_gradient :410-498
+        uint32_t seed = f2u_sat(px) * 324u + u->frame_time * 5632u;
+        float nx = 0.0f, ny = 0.0f;
+        st_walk(u, p, start_indices, px, py, [&](const FluidParticle& q) {
+            const float ox = q.predicted_position[0] - px, oy = q.predicted_position[1] - py;
+            const float sq = ox * ox + oy * oy;
+            if (sq > u->sqr_radius) return;
+            const float dst = sqrtf(sq);
+            float dx, dy;
+            if (dst == 0.0f) {
+                const float rx = st_rand_f32(seed), ry = st_rand_f32(seed);
+                const float len = sqrtf(rx * rx + ry * ry);
+                dx = rx / len; dy = ry / len;
+            } else { dx = ox / dst; dy = oy / dst; }
+            // poly6_kernel_gradient(h, dir) funcs.wgsl:81-88
+            const float r_len = sqrtf(dx * dx + dy * dy);
+            float kx = 0.0f, ky = 0.0f;
+            if (!(r_len >= h || r_len == 0.0f)) {
+                const float diff2 = h * h - r_len * r_len;
+                kx = c_grad * diff2 * diff2 * dx; ky = c_grad * diff2 * diff2 * dy;
+            }
+            const float w = u->particle_mass / q.density;
+            nx += w * kx; ny += w * ky;
+        });
+        const float n_len = sqrtf(nx * nx + ny * ny);
+        float fx = 0.0f, fy = 0.0f;
+        if (n_len > u->surface_tension_treshold) {  // compute.wgsl:304
+            float lap = 0.0f;                        // calculate_colour_field_laplacian :316-405
+            st_walk(u, p, start_indices, px, py, [&](const FluidParticle& q) {
+                const float ox = q.predicted_position[0] - px, oy = q.predicted_position[1] - py;
+                const float sq = ox * ox + oy * oy;
+                if (sq > u->sqr_radius) return;
+                const float dst = sqrtf(sq);
+                float k = 0.0f;
+                if (!(dst > h)) { const float h2 = h * h, r2 = dst * dst; k = c_lap * (h2 - r2) * (3.0f * h2 - 4.0f * r2); }  // funcs.wgsl:91-98
+                lap += (u->particle_mass / q.density) * k;
+            });
+            const float k = (-lap) / (n_len + 1e-6f);
+            const float s = -u->surface_tension_coefficient * k;
+            fx = s * (nx / n_len); fy = s * (ny / n_len);
+        }
+        out_xy[2 * id] = fx; out_xy[2 * id + 1] = fy;
+    }
+}
+
 }  // extern "C"
