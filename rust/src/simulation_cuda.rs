@@ -24,6 +24,10 @@ pub struct TickSettings {
     pub mouse_pos: [f32; 2], pub mouse_state: i32,
 }
 
+/// the reference's storage-buffer record (src/renderer.rs:82-90); its own `FluidObject` can be passed by pointer
+#[repr(C, align(16))] #[derive(Clone, Copy, Debug)]
+pub struct FluidObject { pub position: [f32; 2], pub kind: u32, pub pad: u32, pub pad2: [u32; 4] }
+
 #[repr(C)] pub struct FluidSim { _opaque: [u8; 0] }
 
 extern "C" {
@@ -39,6 +43,11 @@ extern "C" {
     fn fluid_sim_grid_w(sim: *const FluidSim) -> u32;
     fn fluid_sim_grid_h(sim: *const FluidSim) -> u32;
     fn fluid_sim_stream(sim: *mut FluidSim) -> *mut c_void;
+    fn fluid_sim_field_from_objects(sim: *mut FluidSim, objects: *const FluidObject, n: u32, inv_proj: *const f32,
+                                    mask_out: *mut u8, seeds_out: *mut u32, field_xy_out: *mut f32, ms_out: *mut f32) -> c_int;
+    fn fluid_sim_field_from_mask(sim: *mut FluidSim, mask: *const u8, seeds_out: *mut u32, field_xy_out: *mut f32, ms_out: *mut f32) -> c_int;
+    fn fluid_sim_render(sim: *mut FluidSim, inv_proj: *const f32, w: u32, h: u32, rgba_f32_out: *mut f32, rgba8_out: *mut u8, ms_out: *mut f32) -> c_int;
+    fn fluid_sim_surface_tension(sim: *mut FluidSim, force_xy_out: *mut f32) -> c_int;
 }
 
 fn check(rc: c_int) {
@@ -84,6 +93,34 @@ impl FluidSimulation {
         check(unsafe { fluid_sim_download_start_indices(self.handle, v.as_mut_ptr()) });
         v
     }
+    /// row f1 — replaces the object render pass, the texture readback, the CPU field thread and the `write_buffer`
+    /// of src/renderer.rs:449-547: objects -> mask -> seeds -> jump flood -> force field, on the sim's stream, in
+    /// the same frame. `inv_proj` = `self.projection.inverse().to_cols_array()` (src/renderer.rs:450).
+    pub fn set_objects(&mut self, objects: &[FluidObject], inv_proj: &[f32; 16]) {
+        use std::ptr::null_mut;
+        check(unsafe { fluid_sim_field_from_objects(self.handle, objects.as_ptr(), objects.len() as u32, inv_proj.as_ptr(),
+                                                    null_mut(), null_mut(), null_mut(), null_mut()) });
+    }
+    /// the same from a ready mask (the reference's `Image`, src/main.rs:379-399): 0 = obstacle, texture-sized
+    pub fn set_obstacle_mask(&mut self, mask: &[u8]) {
+        use std::ptr::null_mut;
+        assert_eq!(mask.len(), (self.settings.texture_size[0] * self.settings.texture_size[1]) as usize);
+        check(unsafe { fluid_sim_field_from_mask(self.handle, mask.as_ptr(), null_mut(), null_mut(), null_mut()) });
+    }
+    /// row f2 — headless fluid_shader.wgsl (src/renderer.rs:430-462): the blended RGBA8 image, row 0 = top
+    pub fn render_rgba8(&mut self, inv_proj: &[f32; 16], w: u32, h: u32) -> Vec<u8> {
+        let mut img = vec![0u8; (w * h * 4) as usize];
+        check(unsafe { fluid_sim_render(self.handle, inv_proj.as_ptr(), w, h, std::ptr::null_mut(), img.as_mut_ptr(), std::ptr::null_mut()) });
+        img
+    }
+    /// row f4 — compute.wgsl:300-498 per sorted particle; a diagnostic, not applied (the call at :92 is commented out)
+    pub fn surface_tension(&mut self) -> Vec<[f32; 2]> {
+        let mut v = vec![[0f32; 2]; self.settings.particle_count as usize];
+        check(unsafe { fluid_sim_surface_tension(self.handle, v.as_mut_ptr() as *mut f32) });
+        v
+    }
+    /// reference: Renderer::restart_simulation, src/renderer.rs:870-872
+    pub fn restart(&mut self, device_ordinal: i32) { *self = Self::new(device_ordinal, self.settings); }
     pub fn cuda_stream(&mut self) -> *mut c_void { unsafe { fluid_sim_stream(self.handle) } }
 }
 
