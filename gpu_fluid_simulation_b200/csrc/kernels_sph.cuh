@@ -171,10 +171,14 @@ __device__ __forceinline__ float density_walk_global(const DevParams& p, const f
     return density;
 }
 
-// Inner loop of the staged walk, hand-scheduled (15 instructions per candidate: LDS.64, 2 FADD, 2 FMUL, FADD, FSETP,
-// FADD + 4 FMUL of the kernel value computed unconditionally, the one predicated FADD into the sum, address bump,
-// ISETP, BRA). The compiler's version unrolled each span x4 / x2 / x1 with separate remainder loops, so lanes of a
-// warp sat in three different loops per span (ncu: 27.7 warp instructions per particle for ~36 candidates).
+// Inner loop of the staged walk, hand-scheduled, TWO candidates per iteration on the packed f32x2 instructions of
+// sm_100a (FADD2 / FMUL2: two IEEE-rounded fp32 results per issue slot — the walk is issue-bound, not FP-pipe-bound):
+// 2 LDS.64, 2 FADD2 (dx, dy of A and of B), 2 FMUL2, 2 FADD (r2), then packed across the two candidates: FADD2
+// (h2 - r2), 4 FMUL2 (norm * d * d * d, mass *), 2 FSETP, the two predicated FADDs into the sum in visiting order,
+// address bump, 2 ISETP, BRA = 21 instructions per two candidates (the scalar loop took 15 per candidate). An odd
+// span ends with B predicated off (its load stays inside the padded staging buffer). The compiler's own version
+// unrolled each span x4 / x2 / x1 with separate remainder loops, so lanes of a warp sat in three different loops per
+// span (ncu: 27.7 warp instructions per particle for ~36 candidates).
 // Tried and dropped (round 1): re-assigning particles to threads by neighbour count to even out the warps of the
 // force pass — with the scan it made the candidate walk diverge (5.7 -> 5.9 ms), with a scanner/evaluator split it
 // needed CTA-wide barriers per round (7.2 ms).
@@ -182,26 +186,42 @@ __device__ __forceinline__ void density_span(uint32_t addr, uint32_t end, float 
                                              float& density) {
     asm volatile(
         "{\n"
-        ".reg .pred in, go;\n"
-        ".reg .f32 x, y, s, d, k;\n"
+        ".reg .pred ia, ib, vb, go;\n"
+        ".reg .f32 sa, sb, ka, kb;\n"
+        ".reg .b64 me, pa, pb, s2, d2, k2, hh, nn, mm;\n"
+        ".reg .u32 nx;\n"
         "setp.lt.u32 go, %1, %2;\n"
         "@!go bra DENS_DONE;\n"
+        "mov.b64 me, {%3, %4};\n"
+        "mov.b64 hh, {%5, %5};\n"
+        "mov.b64 nn, {%6, %6};\n"
+        "mov.b64 mm, {%7, %7};\n"
         "DENS_LOOP:\n"
         ".pragma \"nounroll\";\n"       // ptxas would re-create the x4 / x2 / x1 remainder structure
-        "ld.shared.v2.f32 {x, y}, [%1];\n"
-        "sub.rn.f32 x, x, %3;\n"
-        "sub.rn.f32 y, y, %4;\n"
-        "mul.rn.f32 x, x, x;\n"
-        "mul.rn.f32 y, y, y;\n"
-        "add.rn.f32 s, x, y;\n"
-        "setp.leu.f32 in, s, %5;\n"      // funcs.wgsl:74: r2 > h2 -> 0; NaN falls through, as there
-        "sub.rn.f32 d, %5, s;\n"
-        "mul.rn.f32 k, %6, d;\n"         // funcs.wgsl:76: norm * d * d * d, left to right
-        "mul.rn.f32 k, k, d;\n"
-        "mul.rn.f32 k, k, d;\n"
-        "mul.rn.f32 k, %7, k;\n"         // funcs.wgsl:189-192: mass * kernel
-        "@in add.rn.f32 %0, %0, k;\n"
-        "add.u32 %1, %1, 8;\n"
+        "ld.shared.b64 pa, [%1];\n"
+        "ld.shared.b64 pb, [%1+8];\n"
+        "add.u32 nx, %1, 8;\n"
+        "sub.rn.f32x2 pa, pa, me;\n"
+        "sub.rn.f32x2 pb, pb, me;\n"
+        "mul.rn.f32x2 pa, pa, pa;\n"
+        "mul.rn.f32x2 pb, pb, pb;\n"
+        "mov.b64 {sa, ka}, pa;\n"
+        "mov.b64 {sb, kb}, pb;\n"
+        "add.rn.f32 sa, sa, ka;\n"
+        "add.rn.f32 sb, sb, kb;\n"
+        "setp.lt.u32 vb, nx, %2;\n"
+        "mov.b64 s2, {sa, sb};\n"
+        "sub.rn.f32x2 d2, hh, s2;\n"
+        "mul.rn.f32x2 k2, nn, d2;\n"    // funcs.wgsl:76: norm * d * d * d, left to right
+        "mul.rn.f32x2 k2, k2, d2;\n"
+        "mul.rn.f32x2 k2, k2, d2;\n"
+        "mul.rn.f32x2 k2, mm, k2;\n"    // funcs.wgsl:189-192: mass * kernel
+        "setp.leu.f32 ia, sa, %5;\n"    // funcs.wgsl:74: r2 > h2 -> 0; NaN falls through, as there
+        "setp.leu.and.f32 ib, sb, %5, vb;\n"
+        "mov.b64 {ka, kb}, k2;\n"
+        "@ia add.rn.f32 %0, %0, ka;\n"
+        "@ib add.rn.f32 %0, %0, kb;\n"
+        "add.u32 %1, %1, 16;\n"
         "setp.lt.u32 go, %1, %2;\n"
         "@go bra DENS_LOOP;\n"
         "DENS_DONE:\n"
@@ -224,7 +244,7 @@ __device__ __forceinline__ float density_walk_staged(const DevParams& p, uint32_
 __global__ void __launch_bounds__(SPH_THREADS)
 k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* __restrict__ keys,
           const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk, float* __restrict__ rho) {
-    __shared__ __align__(128) float2 s_pred[SPH_CAP];
+    __shared__ __align__(128) float2 s_pred[SPH_CAP + 2];  // + pad: the pair loop may load one record past a span
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
     // slab mode: owned particles are [own_begin, own_begin + n) of arrays that also hold halo rows on both sides
