@@ -196,7 +196,8 @@ void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, 
 #define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                     \
     k_force_integrate<DBG, EX><<<blocks, SPH_THREADS, 0, s->stream>>>(p, s->pos_s, s->pred_s, s->vel_s, s->rho, keys,   \
                                                                       s->cell_lb, s->quirk, s->force_field,             \
-                                                                      s->d_frame_time, s->slab_goff_dev, pos_out, vel_out, da, db)
+                                                                      s->d_frame_time, s->slab_goff_dev, s->slab ? nullptr : s->quirk + 2,      \
+                                                                      pos_out, vel_out, da, db)
     if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
     else { if (s->exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
 #undef FLUID_LAUNCH_FORCE
@@ -261,7 +262,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
 
     const uint32_t gblocks = (n + GATHER_THREADS - 1) / GATHER_THREADS;
     k_gather_cells<<<gblocks, GATHER_THREADS, 0, stream>>>(p, keys_sorted, idx_sorted, pos_a, vel_a, pos_s, pred_s, vel_s,
-                                                         start_indices, cell_lb, quirk);
+                                                         start_indices, cell_lb, quirk, d_frame_time);
     launches++;
     mark("gather+cells");
     if (hash_sort_only) {
@@ -274,7 +275,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
         return FLUID_OK;
     }
     const uint32_t sblocks = (n + SPH_THREADS - 1) / SPH_THREADS;
-    k_density<<<sblocks, SPH_THREADS, 0, stream>>>(p, pred_s, keys_sorted, cell_lb, quirk, rho);
+    k_density<<<sblocks, SPH_THREADS, 0, stream>>>(p, pred_s, keys_sorted, cell_lb, quirk, rho, quirk + 2, d_frame_time);
     launches++;
     mark("density");
     launch_force(this, p, sblocks, pos_a, vel_a);

@@ -44,7 +44,8 @@ __global__ void __launch_bounds__(GATHER_THREADS)
 k_gather_cells(const DevParams p, const uint32_t* __restrict__ sorted_keys, const uint32_t* __restrict__ sorted_idx,
                const float2* __restrict__ pos_in, const float2* __restrict__ vel_in,
                float2* __restrict__ pos_s, float2* __restrict__ pred_s, float2* __restrict__ vel_s,
-               uint32_t* __restrict__ start_indices, uint32_t* __restrict__ cell_lb, uint32_t* __restrict__ quirk) {
+               uint32_t* __restrict__ start_indices, uint32_t* __restrict__ cell_lb, uint32_t* __restrict__ quirk,
+               const uint32_t* __restrict__ frame_time) {
     const uint32_t i = blockIdx.x * GATHER_THREADS + threadIdx.x;  // grid is a whole number of warps
     const bool valid = i < p.n;
     uint32_t gap_begin = 0, gap_end = 0, gap_value = 0;
@@ -55,7 +56,11 @@ k_gather_cells(const DevParams p, const uint32_t* __restrict__ sorted_keys, cons
         const float2 vs = __ldg(vel_in + src);
         pos_s[i] = ps;
         vel_s[i] = vs;
-        pred_s[i] = predict_position(p, ps, vs);  // same inputs, same ops as the hash pass: same bits
+        const float2 pr = predict_position(p, ps, vs);  // same inputs, same ops as the hash pass: same bits
+        pred_s[i] = pr;
+        // quirk[2] = wild stamp (common.cuh tame_component): any writer stores the same tick number
+        if (!(tame_component(pr.x) && tame_component(pr.y) && tame_component(vs.x) && tame_component(vs.y)))
+            quirk[2] = __ldg(frame_time);
 
         const uint32_t kc = min(k, p.num_cells - 1u);
         if (i == 0) {

@@ -243,7 +243,8 @@ __device__ __forceinline__ float density_walk_staged(const DevParams& p, uint32_
 
 __global__ void __launch_bounds__(SPH_THREADS)
 k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* __restrict__ keys,
-          const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk, float* __restrict__ rho) {
+          const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk, float* __restrict__ rho,
+          uint32_t* __restrict__ wild_stamp /* null: slab mode */, const uint32_t* __restrict__ frame_time) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP + 2];  // + pad: the pair loop may load one record past a span
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
@@ -279,7 +280,11 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
         d = density_walk_global(p, pred_s, a, b, me.x, me.y);
     }
     // funcs.wgsl:202 max(density, EPSILON); compute.wgsl:70 max(.., 0.1)
-    if (valid) rho[i] = fmaxf(fmaxf(d, 1.19209290e-07f), 0.1f);
+    if (valid) {
+        const float dens = fmaxf(fmaxf(d, 1.19209290e-07f), 0.1f);
+        rho[i] = dens;
+        if (wild_stamp && !(dens <= DIV_DEN_HI)) *wild_stamp = __ldg(frame_time);  // common.cuh tame_component
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -319,7 +324,8 @@ struct ForceAcc {
 // per-thread loop invariants of the exact pair body: refined reciprocals of the two constant denominators
 struct PairConsts {
     float y_two_h3, y_h2;
-    bool fast_div;  // h2, two_h3 in the shared-reciprocal range (else every pair takes the __fdiv_rn body)
+    bool fast_div;    // h2, two_h3 in the shared-reciprocal range (else every pair takes the __fdiv_rn body)
+    bool tn_bounded;  // h c_s |k_p| (2^20 + |rho_0|) <= 2^98: no pressure numerator of a tame tick can exceed 2^100
 };
 __device__ __forceinline__ PairConsts make_pair_consts(const DevParams& p) {
     PairConsts c;
@@ -327,7 +333,47 @@ __device__ __forceinline__ PairConsts make_pair_consts(const DevParams& p) {
     c.y_h2 = rcp_refined(p.h2);
     c.fast_div = p.two_h3 >= DIV_DEN_LO && p.two_h3 <= DIV_DEN_HI && p.h2 >= DIV_DEN_LO && p.h2 <= DIV_DEN_HI &&
                  p.h >= DIV_DEN_LO && p.h <= DIV_DEN_HI;
+    c.tn_bounded = fabsf(p.h * p.spiky) * fabsf(p.pressure_constant) * (DIV_DEN_HI + fabsf(p.rest_density)) <= 3.1691265e29f;
     return c;
+}
+
+// the pair body with IEEE division throughout (== the CPU restatement operation for operation): taken by pairs whose
+// operands fall outside the shared-reciprocal range, including the coincident-particle RNG branch
+struct SlowConsts { float h, h2, two_h3, visc_k; };  // by value: a DevParams reference would force a local copy
+struct SlowTerms { float tx, ty, ux, uy; uint32_t seed; };  // by value: references would go through the stack
+__device__ __noinline__ SlowTerms force_pair_slow_call(const SlowConsts p, float dx, float dy, float dst, float k, float shared_p,
+                                                       float dvx, float dvy, float nd, uint32_t rand_seed) {
+    float tx, ty, ux, uy;
+    float sdirx, sdiry;
+    if (dst == 0.0f) {  // compute.wgsl:211-212
+        const float rx = rand_f32(rand_seed);
+        const float ry = rand_f32(rand_seed);
+        const float len = fsqrt(fadd(fmul(rx, rx), fmul(ry, ry)));
+        sdirx = fdiv(rx, len); sdiry = fdiv(ry, len);
+    } else {
+        sdirx = fdiv(dx, dst); sdiry = fdiv(dy, dst);
+    }
+    tx = fdiv(fmul(fmul(sdirx, k), shared_p), nd);
+    ty = fdiv(fmul(fmul(sdiry, k), shared_p), nd);
+    float skv = 0.0f;  // funcs.wgsl:112-123
+    if (dst <= p.h) {
+        if (dst == 0.0f) skv = p.visc_k;
+        else {
+            const float A = fdiv(-fmul(fmul(dst, dst), dst), p.two_h3);
+            const float B = fdiv(fmul(dst, dst), p.h2);
+            const float C = fdiv(p.h, fmul(2.0f, dst));
+            skv = fmul(p.visc_k, fsub(fadd(fadd(A, B), C), 1.0f));
+        }
+    }
+    ux = fmul(fdiv(dvx, nd), skv);
+    uy = fmul(fdiv(dvy, nd), skv);
+    return SlowTerms{tx, ty, ux, uy, rand_seed};
+}
+__device__ __forceinline__ void force_pair_slow(const SlowConsts p, float dx, float dy, float dst, float k, float shared_p,
+                                                float dvx, float dvy, float nd, uint32_t& rand_seed, float& tx, float& ty,
+                                                float& ux, float& uy) {
+    const SlowTerms t = force_pair_slow_call(p, dx, dy, dst, k, shared_p, dvx, dvy, nd, rand_seed);
+    tx = t.tx; ty = t.ty; ux = t.ux; uy = t.uy; rand_seed = t.seed;
 }
 
 template <bool DEBUG, bool EXACT>
@@ -360,22 +406,7 @@ __device__ __forceinline__ void force_pair(const DevParams& p, const PairConsts&
         const int safe = (int)c.fast_div & (int)(sq >= DIV_DEN_LO * DIV_DEN_LO) & (int)(nd >= DIV_DEN_LO) &
                          (int)(nd <= DIV_DEN_HI) & div_num_lo_ok(dx) & div_num_lo_ok(dy) & div_num_ok(dvx) &
                          div_num_ok(dvy) & div_num_ok(tnx) & div_num_ok(tny);
-        if (!safe) {
-            float sdirx, sdiry;
-            if (dst == 0.0f) {  // compute.wgsl:211-212
-                const float rx = rand_f32(rand_seed);
-                const float ry = rand_f32(rand_seed);
-                const float len = fsqrt(fadd(fmul(rx, rx), fmul(ry, ry)));
-                sdirx = fdiv(rx, len); sdiry = fdiv(ry, len);
-            } else {
-                sdirx = fdiv(dx, dst); sdiry = fdiv(dy, dst);
-            }
-            tx = fdiv(fmul(fmul(sdirx, k), shared_p), nd);
-            ty = fdiv(fmul(fmul(sdiry, k), shared_p), nd);
-            const float skv = viscosity_kernel(p, dst);
-            ux = fmul(fdiv(dvx, nd), skv);
-            uy = fmul(fdiv(dvy, nd), skv);
-        }
+        if (!safe) force_pair_slow(SlowConsts{p.h, p.h2, p.two_h3, p.visc_k}, dx, dy, dst, k, shared_p, dvx, dvy, nd, rand_seed, tx, ty, ux, uy);
         acc.px = fadd(acc.px, tx);
         acc.py = fadd(acc.py, ty);
         acc.vx = fadd(acc.vx, ux);
@@ -415,6 +446,90 @@ __device__ __forceinline__ void force_pair(const DevParams& p, const PairConsts&
     }
 }
 
+// Two accepted neighbours (A, then B in visiting order) per call, every operation of the exact body packed across
+// the two (common.cuh f32x2): the same IEEE-rounded operations in the same order per neighbour, so the same bits, at
+// about half the issue slots. hasB = false evaluates A twice and drops the copy. A neighbour outside the
+// shared-reciprocal range takes force_pair_slow; the terms are added A first, then B (compute.wgsl:206-223, :283-288).
+template <bool DEBUG>
+__device__ __forceinline__ void force_pair2(const DevParams& p, const PairConsts& c, float dxA, float dyA, float dxB, float dyB,
+                                            float2 nvA, float2 nvB, float ndA, float ndB, bool hasB, bool tame, float vx, float vy,
+                                            float pressure, uint32_t& rand_seed, ForceAcc& acc) {
+    const f32x2 dx = pk2(dxA, dxB), dy = pk2(dyA, dyB), nd = pk2(ndA, ndB);
+    const float dvxA = fsub(nvA.x, vx), dvyA = fsub(nvA.y, vy), dvxB = fsub(nvB.x, vx), dvyB = fsub(nvB.y, vy);
+    const f32x2 dvx = pk2(dvxA, dvxB), dvy = pk2(dvyA, dvyB);
+    // ptxas (12.9) contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 even though both carry .rn (and under -fmad=false);
+    // a sum whose addend is an inexact packed product is therefore taken with scalar FADDs (add2_of_products)
+    const f32x2 sq = add2_of_products(mul2(dx, dx), mul2(dy, dy));
+    const f32x2 dst = sqrt2_inrange(sq);
+    const f32x2 np = mul2(bc2(p.pressure_constant), sub2(nd, bc2(p.rest_density)));
+    const f32x2 shared_p = mul2(add2_of_products(bc2(pressure), np), bc2(0.5f));
+    const bool inA = lo2(dst) <= p.h, inB = hi2(dst) <= p.h;
+    const f32x2 kraw = mul2(sub2(bc2(p.h), dst), bc2(-p.spiky));  // -(h - r) * c_s, funcs.wgsl:101-109
+    const float kA = inA ? lo2(kraw) : 0.0f, kB = inB ? hi2(kraw) : 0.0f;
+    const f32x2 k = pk2(kA, kB);
+    const f32x2 yr = rcp_refined2(dst), yd = rcp_refined2(nd);
+    const f32x2 dirx = div_by2(dx, dst, yr), diry = div_by2(dy, dst, yr);
+    const f32x2 tnx = mul2(mul2(dirx, k), shared_p), tny = mul2(mul2(diry, k), shared_p);
+    const f32x2 tx2 = div_by2(tnx, nd, yd), ty2 = div_by2(tny, nd, yd);
+    const f32x2 r2 = mul2(dst, dst);
+    const f32x2 r3 = mul2(r2, dst);
+    const f32x2 A = div_by2(neg2(r3), bc2(p.two_h3), bc2(c.y_two_h3));
+    const f32x2 B = div_by2(r2, bc2(p.h2), bc2(c.y_h2));
+    // (A + B) + h / (2 r): the halving is exact (h / r >= 1 here), so fusing it into the addition rounds the same sum
+    const f32x2 ABC = fma2(div_by2(bc2(p.h), dst, yr), bc2(0.5f), add2(A, B));
+    const f32x2 kvraw = mul2(bc2(p.visc_k), sub2(ABC, bc2(1.0f)));  // funcs.wgsl:112-123
+    const float kvA = inA ? lo2(kvraw) : 0.0f, kvB = inB ? hi2(kvraw) : 0.0f;
+    const f32x2 kv = pk2(kvA, kvB);
+    const f32x2 ux2 = mul2(div_by2(dvx, nd, yd), kv), uy2 = mul2(div_by2(dvy, nd, yd), kv);  // compute.wgsl:288
+    float txA = lo2(tx2), tyA = lo2(ty2), uxA = lo2(ux2), uyA = lo2(uy2);
+    float txB = hi2(tx2), tyB = hi2(ty2), uxB = hi2(ux2), uyB = hi2(uy2);
+    // range tests of the shared-reciprocal quotients (common.cuh div_by). With tame inputs (the tick's stamp) only
+    // r >= 2^-20 and the lower bound of the pressure numerators are left to test per pair; their upper bound is
+    // c.tn_bounded: |dir| <= 1, |k| <= h c_s, |shared pressure| <= |k_p| (2^20 + |rho_0|).
+    int safeA = (int)c.fast_div & (int)(lo2(sq) >= DIV_DEN_LO * DIV_DEN_LO) & div_num_lo_ok(lo2(tnx)) & div_num_lo_ok(lo2(tny));
+    int safeB = (int)c.fast_div & (int)(hi2(sq) >= DIV_DEN_LO * DIV_DEN_LO) & div_num_lo_ok(hi2(tnx)) & div_num_lo_ok(hi2(tny));
+    if (!(tame && c.tn_bounded)) {
+        safeA &= (int)(ndA >= DIV_DEN_LO) & (int)(ndA <= DIV_DEN_HI) & div_num_lo_ok(dxA) & div_num_lo_ok(dyA) & div_num_ok(dvxA) &
+                 div_num_ok(dvyA) & div_num_ok(lo2(tnx)) & div_num_ok(lo2(tny));
+        safeB &= (int)(ndB >= DIV_DEN_LO) & (int)(ndB <= DIV_DEN_HI) & div_num_lo_ok(dxB) & div_num_lo_ok(dyB) & div_num_ok(dvxB) &
+                 div_num_ok(dvyB) & div_num_ok(hi2(tnx)) & div_num_ok(hi2(tny));
+    }
+    if (!(safeA & safeB)) {
+        if (!safeA) {
+            const float sqA = fadd(fmul(dxA, dxA), fmul(dyA, dyA));
+            const float dstA = fsqrt(sqA);
+            const float kk = (dstA <= p.h) ? fmul(-fsub(p.h, dstA), p.spiky) : 0.0f;
+            const float sp = fmul(fadd(pressure, fmul(p.pressure_constant, fsub(ndA, p.rest_density))), 0.5f);
+            force_pair_slow(SlowConsts{p.h, p.h2, p.two_h3, p.visc_k}, dxA, dyA, dstA, kk, sp, dvxA, dvyA, ndA, rand_seed, txA, tyA, uxA, uyA);
+        }
+        if (hasB && !safeB) {
+            const float sqB = fadd(fmul(dxB, dxB), fmul(dyB, dyB));
+            const float dstB = fsqrt(sqB);
+            const float kk = (dstB <= p.h) ? fmul(-fsub(p.h, dstB), p.spiky) : 0.0f;
+            const float sp = fmul(fadd(pressure, fmul(p.pressure_constant, fsub(ndB, p.rest_density))), 0.5f);
+            force_pair_slow(SlowConsts{p.h, p.h2, p.two_h3, p.visc_k}, dxB, dyB, dstB, kk, sp, dvxB, dvyB, ndB, rand_seed, txB, tyB, uxB, uyB);
+        }
+    }
+    acc.px = fadd(acc.px, txA);
+    acc.py = fadd(acc.py, tyA);
+    acc.vx = fadd(acc.vx, uxA);
+    acc.vy = fadd(acc.vy, uyA);
+    if (DEBUG) {
+        acc.ax += fabsf(txA) + fabsf(uxA) * p.visc_coef;
+        acc.ay += fabsf(tyA) + fabsf(uyA) * p.visc_coef;
+    }
+    if (hasB) {
+        acc.px = fadd(acc.px, txB);
+        acc.py = fadd(acc.py, tyB);
+        acc.vx = fadd(acc.vx, uxB);
+        acc.vy = fadd(acc.vy, uyB);
+        if (DEBUG) {
+            acc.ax += fabsf(txB) + fabsf(uxB) * p.visc_coef;
+            acc.ay += fabsf(tyB) + fabsf(uyB) * p.visc_coef;
+        }
+    }
+}
+
 // fallback walk straight from global memory (CTAs whose neighbourhood does not fit the staging buffer)
 template <bool DEBUG, bool EXACT>
 __device__ __forceinline__ void force_walk_global(const DevParams& p, const float2* __restrict__ pred,
@@ -447,7 +562,7 @@ __device__ __forceinline__ void force_walk_global(const DevParams& p, const floa
 #define FLUID_FORCE_LIST 16
 #endif
 #ifndef FLUID_FORCE_MIN_CTAS
-#define FLUID_FORCE_MIN_CTAS 1
+#define FLUID_FORCE_MIN_CTAS 4
 #endif
 constexpr int FORCE_LIST = FLUID_FORCE_LIST;
 
@@ -494,7 +609,7 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
                                                   uint32_t list_addr /* this thread's column of [FORCE_LIST][SPH_THREADS] u16 */,
                                                   const int (&base)[3], const uint32_t (&a)[3], const uint32_t (&b)[3],
                                                   uint32_t self, float px, float py, float vx, float vy, float pressure,
-                                                  uint32_t& rand_seed, ForceAcc& acc) {
+                                                  bool tame, uint32_t& rand_seed, ForceAcc& acc) {
     const PairConsts pc = make_pair_consts(p);
     // four spans in visiting order: row y-1; row y before self; row y after self (compute.wgsl:195 skips self by
     // index; a particle lies inside its own row's span unless the stale-entry quirk moved the span start past it); row y+1
@@ -523,15 +638,31 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
         // ---- phase B: evaluate ----
         const uint32_t cnt_bytes = wr - list_addr;
         const uint32_t max_bytes = __reduce_max_sync(0xffffffffu, cnt_bytes);
-        for (uint32_t k = 0; k < max_bytes; k += SPH_THREADS * 2u) {
-            if (k < cnt_bytes) {
-                const uint32_t e = lds_u16(list_addr + k);
-                const float2 q = lds_f2(e);
-                const float2 nv = lds_f2(e + vel_delta);
-                const float nd = lds_f((e >> 1) + rho_base);
-                const float dx = fsub(q.x, px), dy = fsub(q.y, py);
-                const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
-                force_pair<DEBUG, EXACT>(p, pc, dx, dy, sq, nv, nd, vx, vy, pressure, rand_seed, acc);
+        if (EXACT) {
+            // two list entries per iteration (force_pair2); an odd list ends with B = A, dropped
+            for (uint32_t k = 0; k < max_bytes; k += SPH_THREADS * 4u) {
+                if (k < cnt_bytes) {
+                    const bool hasB = k + SPH_THREADS * 2u < cnt_bytes;
+                    const uint32_t eA = lds_u16(list_addr + k);
+                    const uint32_t eB = hasB ? lds_u16(list_addr + k + SPH_THREADS * 2u) : eA;
+                    const float2 qA = lds_f2(eA), qB = lds_f2(eB);
+                    const float2 nvA = lds_f2(eA + vel_delta), nvB = lds_f2(eB + vel_delta);
+                    const float ndA = lds_f((eA >> 1) + rho_base), ndB = lds_f((eB >> 1) + rho_base);
+                    force_pair2<DEBUG>(p, pc, fsub(qA.x, px), fsub(qA.y, py), fsub(qB.x, px), fsub(qB.y, py), nvA, nvB, ndA, ndB,
+                                       hasB, tame, vx, vy, pressure, rand_seed, acc);
+                }
+            }
+        } else {
+            for (uint32_t k = 0; k < max_bytes; k += SPH_THREADS * 2u) {
+                if (k < cnt_bytes) {
+                    const uint32_t e = lds_u16(list_addr + k);
+                    const float2 q = lds_f2(e);
+                    const float2 nv = lds_f2(e + vel_delta);
+                    const float nd = lds_f((e >> 1) + rho_base);
+                    const float dx = fsub(q.x, px), dy = fsub(q.y, py);
+                    const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
+                    force_pair<DEBUG, EXACT>(p, pc, dx, dy, sq, nv, nd, vx, vy, pressure, rand_seed, acc);
+                }
             }
         }
         __syncwarp();
@@ -545,6 +676,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
                   const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk,
                   const float2* __restrict__ force_field, const uint32_t* __restrict__ frame_time,
                   const uint32_t* __restrict__ global_offset_dev /* slab mode with device-resolved metadata, else null */,
+                  const uint32_t* __restrict__ wild_stamp /* null: always take the per-pair range tests */,
                   float2* __restrict__ pos_out, float2* __restrict__ vel_out, float2* __restrict__ dbg_accel,
                   float2* __restrict__ dbg_abs) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP];
@@ -578,6 +710,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
         dens = __ldg(rho + i);
     }
     const uint32_t ft = __ldg(frame_time);
+    const bool tame = wild_stamp != nullptr && __ldg(wild_stamp) != ft;  // common.cuh tame_component
     const uint32_t out_i = i - p.own_begin;                      // index in the (halo-free) state arrays
     const uint32_t goff = p.global_offset + (global_offset_dev ? __ldg(global_offset_dev) : 0u);
     uint32_t rand_seed = (out_i + goff) * 12u + ft * 69u;  // compute.wgsl:161 (global sorted index)
@@ -589,7 +722,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
         int base[3];
         thread_bases(s_plan, valid ? cy : s_plan.row_first, base);
         force_walk_staged<DEBUG, EXACT>(p, smem_u32_pinned(s_pred), smem_u32_pinned(s_vel), smem_u32_pinned(s_rho), smem_u32_pinned(s_list + threadIdx.x),
-                                        base, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
+                                        base, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, tame, rand_seed, acc);
     } else {
         force_walk_global<DEBUG, EXACT>(p, pred_s, vel_s, rho, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
     }

@@ -112,6 +112,27 @@ def test_all_particles_in_one_cell_and_exact_duplicates(fluid, oracle):
     assert stats["floats_bit_exact"], stats
 
 
+@pytest.mark.parametrize("wild", ["tiny_velocity", "tiny_offset", "huge_mass", "none"])
+def test_range_tested_path_for_wild_inputs(fluid, oracle, wild):
+    """the force pass skips most per-pair range tests of its shared-reciprocal divisions when the tick's inputs are
+    "tame" (components zero or in [2^-70, 2^99], densities <= 2^20: stamped by the gather and density passes). One wild
+    value anywhere must send the whole tick through the fully range-tested body — same bits either way."""
+    s, ts, p = scenes.uniform_box(64)
+    if wild == "tiny_velocity":
+        p["velocity"][1234] = [3e-30, -7e-33]          # differences of ~1e-30: below the 2^-100 numerator bound
+        p["velocity"][1235] = [0.0, 1e-38]
+    elif wild == "tiny_offset":
+        # two particles 1e-30 apart in x next to the origin: dx tiny but non-zero, r < 2^-20
+        p["position"][2000] = [1e-30, 2e-31]
+        p["position"][2001] = [2e-30, 2e-31]
+        p["predicted_position"][2000:2002] = p["position"][2000:2002]
+        p["velocity"][2000:2002] = 0
+    elif wild == "huge_mass":
+        ts = TickSettings(**{**ts.__dict__, "mass": 3e8})  # densities above 2^20
+    stats = _check(fluid, oracle, s, ts, p, n_ticks=2)
+    assert stats["floats_bit_exact"], stats
+
+
 def test_walls_speed_clamp_and_nan_guard(fluid, oracle):
     n = 2048
     s = SimulationSettings(particle_count=n, size=(8.0, 8.0), texture_size=(8, 8))
