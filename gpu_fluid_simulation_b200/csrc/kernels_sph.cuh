@@ -602,6 +602,54 @@ __device__ __forceinline__ void scan_span(uint32_t& addr, uint32_t end, uint32_t
         : "r"(end), "r"(wr_end), "f"(px), "f"(py), "f"(h2)
         : "memory");
 }
+// the same scan, two candidates per iteration on packed subtract / multiply (see density_span), while at least two
+// candidates and two list slots remain; scan_span finishes the span. 21 instructions per two candidates.
+__device__ __forceinline__ void scan_span2(uint32_t& addr, uint32_t end, uint32_t& wr, uint32_t wr_end, float px, float py,
+                                           float h2) {
+    asm volatile(
+        "{\n"
+        ".reg .pred ha, hb, go;\n"
+        ".reg .f32 sa, sb, ta, tb;\n"
+        ".reg .b64 me, pa, pb;\n"
+        ".reg .b16 la, lb;\n"
+        ".reg .u32 nx, e2, w2;\n"
+        "add.u32 e2, %2, -8;\n"
+        "add.u32 w2, %3, -512;\n"
+        "setp.lt.s32 go, %0, e2;\n"          // shared-window addresses are < 2^31: signed compare survives end - 8 < 0
+        "setp.lt.and.s32 go, %1, w2, go;\n"
+        "@!go bra SCAN2_DONE;\n"
+        "mov.b64 me, {%4, %5};\n"
+        "SCAN2_LOOP:\n"
+        ".pragma \"nounroll\";\n"
+        "ld.shared.b64 pa, [%0];\n"
+        "ld.shared.b64 pb, [%0+8];\n"
+        "add.u32 nx, %0, 8;\n"
+        "sub.rn.f32x2 pa, pa, me;\n"
+        "sub.rn.f32x2 pb, pb, me;\n"
+        "mul.rn.f32x2 pa, pa, pa;\n"
+        "mul.rn.f32x2 pb, pb, pb;\n"
+        "mov.b64 {sa, ta}, pa;\n"
+        "mov.b64 {sb, tb}, pb;\n"
+        "add.rn.f32 sa, sa, ta;\n"
+        "add.rn.f32 sb, sb, tb;\n"
+        "setp.leu.f32 ha, sa, %6;\n"
+        "setp.leu.f32 hb, sb, %6;\n"
+        "cvt.u16.u32 la, %0;\n"
+        "cvt.u16.u32 lb, nx;\n"
+        "@ha st.shared.u16 [%1], la;\n"
+        "@ha add.u32 %1, %1, 512;\n"
+        "@hb st.shared.u16 [%1], lb;\n"
+        "@hb add.u32 %1, %1, 512;\n"
+        "add.u32 %0, %0, 16;\n"
+        "setp.lt.s32 go, %0, e2;\n"
+        "setp.lt.and.s32 go, %1, w2, go;\n"
+        "@go bra SCAN2_LOOP;\n"
+        "SCAN2_DONE:\n"
+        "}\n"
+        : "+r"(addr), "+r"(wr)
+        : "r"(end), "r"(wr_end), "f"(px), "f"(py), "f"(h2)
+        : "memory");
+}
 static_assert(SPH_THREADS * 2 == 512, "scan_span hard-codes the list column stride");
 
 template <bool DEBUG, bool EXACT>
@@ -627,6 +675,7 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
         uint32_t wr = list_addr;
         // ---- phase A: scan ----
         while (more) {
+            scan_span2(addr, end, wr, wr_end, px, py, p.h2);
             scan_span(addr, end, wr, wr_end, px, py, p.h2);
             if (addr < end) break;  // list full: evaluate it, then resume this span
             if (r == 0) { addr = A1; end = S1; r = 1; }
