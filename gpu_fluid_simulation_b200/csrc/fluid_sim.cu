@@ -82,7 +82,7 @@ int Sim::alloc(uint32_t cap) {
     // free old particle-sized buffers, allocate new; contents are NOT preserved
     void** bufs[] = {(void**)&pos_a, (void**)&vel_a, (void**)&pos_s, (void**)&vel_s, (void**)&pred_s, (void**)&rho,
                      (void**)&keys_u, (void**)&keys_b, (void**)&keys_c, (void**)&idx_a, (void**)&idx_b,
-                     (void**)&sort_scratch, (void**)&aos_stage, (void**)&dbg_accel, (void**)&dbg_abs};
+                     (void**)&sort_scratch, (void**)&aos_stage, (void**)&dbg_accel, (void**)&dbg_abs, (void**)&tile_plans};
     for (void** b : bufs) { if (*b) cudaFree(*b); *b = nullptr; }
     capacity = cap;
     const size_t padded = (size_t)cap + 64;
@@ -100,6 +100,7 @@ int Sim::alloc(uint32_t cap) {
     // [hist MAX_PASSES*256][tile counters MAX_PASSES, padded to 256][status MAX_PASSES*max_tiles*256]
     sort_scratch_words = (size_t)MAX_PASSES * RADIX + RADIX + (size_t)MAX_PASSES * max_tiles * RADIX;
     FLUID_CUDA(cudaMalloc(&sort_scratch, sort_scratch_words * 4));
+    FLUID_CUDA(cudaMalloc(&tile_plans, ((size_t)cap / SPH_THREADS + 2) * sizeof(TilePlan)));
     keys_sorted = keys_b;
     return FLUID_OK;
 }
@@ -189,6 +190,14 @@ void Sim::mark(const char* name) {
     n_marks++;
 }
 
+// staging plans of the two neighbour passes (kernels_sph.cuh TilePlan), once per tick after the cell table is complete
+void launch_tile_plans(Sim* s, const DevParams& p, const uint32_t* keys) {
+    const uint32_t ntiles = (p.n + SPH_THREADS - 1) / SPH_THREADS;
+    if (!ntiles) return;
+    k_tile_plans<<<(ntiles + 127) / 128, 128, 0, s->stream>>>(p, keys, s->cell_lb, ntiles, reinterpret_cast<TilePlan*>(s->tile_plans));
+    s->launches++;
+}
+
 void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, float2* vel_out) {
     float2* da = s->debug_force ? s->dbg_accel : nullptr;
     float2* db = s->debug_force ? s->dbg_abs : nullptr;
@@ -197,6 +206,7 @@ void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, 
     k_force_integrate<DBG, EX><<<blocks, SPH_THREADS, 0, s->stream>>>(p, s->pos_s, s->pred_s, s->vel_s, s->rho, keys,   \
                                                                       s->cell_lb, s->quirk, s->force_field,             \
                                                                       s->d_frame_time, s->slab_goff_dev, s->slab ? nullptr : s->quirk + 2,      \
+                                                                      reinterpret_cast<const TilePlan*>(s->tile_plans),                 \
                                                                       pos_out, vel_out, da, db)
     if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
     else { if (s->exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
@@ -275,7 +285,9 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
         return FLUID_OK;
     }
     const uint32_t sblocks = (n + SPH_THREADS - 1) / SPH_THREADS;
-    k_density<<<sblocks, SPH_THREADS, 0, stream>>>(p, pred_s, keys_sorted, cell_lb, quirk, rho, quirk + 2, d_frame_time);
+    launch_tile_plans(this, p, keys_sorted);
+    k_density<<<sblocks, SPH_THREADS, 0, stream>>>(p, pred_s, keys_sorted, cell_lb, quirk, rho, quirk + 2, d_frame_time,
+                                                   reinterpret_cast<const TilePlan*>(tile_plans));
     launches++;
     mark("density");
     launch_force(this, p, sblocks, pos_a, vel_a);
@@ -383,7 +395,7 @@ void fluid_sim_destroy(FluidSim* h) {
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
-                    s->idx_b, s->sort_scratch, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
+                    s->idx_b, s->sort_scratch, s->tile_plans, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
                     s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta,
                     s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn};
     for (void* b : bufs) if (b) cudaFree(b);

@@ -39,18 +39,31 @@ struct SpanPlan {
     int staged;  // 1: spans are in shared memory; 0: walk global memory
 };
 
-// thread-0 planning: which global index intervals does this CTA need, do they fit, issue the copies.
-// arrays[k] / smem[k] / elem_bytes[k]: the SoA streams to stage (1 for density, 3 for force).
-//   * CTA within <= SPH_MAX_ROWS grid rows: per row group g, the cells [x_lo-1, x_hi+1] of rows y-1, y, y+1,
-//     where [x_lo, x_hi] bounds the CTA's particles of that row (3 spans per group);
+// Per-tile staging plan, computed once per tick by k_tile_plans (one thread per tile of SPH_THREADS sorted particles)
+// and consumed by thread 0 of the density and force CTAs: which global index intervals the tile needs and whether
+// they fit. Keeping the key / table look-ups out of the CTAs shortens their start-up chain from three dependent
+// global-memory latencies (keys -> table -> TMA) to two (plan -> TMA).
+//   * tile within <= SPH_MAX_ROWS grid rows: per row group g, the cells [x_lo-1, x_hi+1] of rows y-1, y, y+1,
+//     where [x_lo, x_hi] bounds the tile's particles of that row (3 spans per group);
 //   * more rows (short rows): one span from (first row - 1, x_first - 1) to (last row + 1, x_last + 1);
 //   * if the spans exceed SPH_CAP particles the CTA walks global memory instead.
-template <int NARR>
-__device__ __forceinline__ void plan_and_stage(const DevParams& p, uint32_t i0, uint32_t i1,
-                                               const uint32_t* __restrict__ keys, const uint32_t* __restrict__ lb,
-                                               const void* const (&arrays)[NARR], void* const (&smem)[NARR],
-                                               const uint32_t (&elem_bytes)[NARR], uint64_t* bar, SpanPlan* plan) {
+struct __align__(16) TilePlan {
+    uint32_t lo[SPH_MAX_ROWS * 3];   // first particle of each span (multiple of 4: 16-byte granularity for every stream)
+    uint32_t len[SPH_MAX_ROWS * 3];  // particles per span (multiple of 4)
+    uint32_t row_first;
+    uint32_t flags;                  // bit 0: staged, bit 1: grouped
+    uint32_t pad[2];
+};
+static_assert(sizeof(TilePlan) == 64, "TilePlan is read as four 16-byte words");
+
+__global__ void __launch_bounds__(128)
+k_tile_plans(const DevParams p, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ lb, uint32_t ntiles,
+             TilePlan* __restrict__ plans) {
     constexpr int NI = SPH_MAX_ROWS * 3;
+    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile >= ntiles) return;
+    const uint32_t i0 = p.own_begin + tile * SPH_THREADS;
+    const uint32_t i1 = min(i0 + SPH_THREADS, p.own_begin + p.n);
     const uint32_t kf = min(__ldg(keys + i0), p.num_cells - 1u), kl = min(__ldg(keys + i1 - 1u), p.num_cells - 1u);
     const uint32_t yf = kf / p.grid_w, xa = kf - yf * p.grid_w;
     const uint32_t yl = kl / p.grid_w, xb = kl - yl * p.grid_w;
@@ -58,7 +71,6 @@ __device__ __forceinline__ void plan_and_stage(const DevParams& p, uint32_t i0, 
     uint32_t lo[NI], hi[NI];
 #pragma unroll
     for (int t = 0; t < NI; t++) { lo[t] = 0; hi[t] = 0; }
-    plan->row_first = yf;
     const bool grouped = nrows <= (uint32_t)SPH_MAX_ROWS;
     if (grouped) {
 #pragma unroll
@@ -83,35 +95,61 @@ __device__ __forceinline__ void plan_and_stage(const DevParams& p, uint32_t i0, 
         lo[0] = __ldg(lb + ca);
         hi[0] = __ldg(lb + cb);
     }
-    // 16-byte granularity for every stream: round to multiples of 4 particles
-    uint32_t total = 0, off[NI];
+    TilePlan out;
+    uint32_t total = 0;
 #pragma unroll
     for (int t = 0; t < NI; t++) {
         lo[t] &= ~3u;
         hi[t] = (hi[t] + 3u) & ~3u;
         if (hi[t] < lo[t]) hi[t] = lo[t];
-        off[t] = total;
+        out.lo[t] = lo[t];
+        out.len[t] = hi[t] - lo[t];
         total += hi[t] - lo[t];
     }
-    if (total > (uint32_t)SPH_CAP) {
+    out.row_first = yf;
+    out.flags = (total <= (uint32_t)SPH_CAP ? 1u : 0u) | (grouped ? 2u : 0u);
+    out.pad[0] = 0; out.pad[1] = 0;
+    const uint4* src = reinterpret_cast<const uint4*>(&out);
+    uint4* dst = reinterpret_cast<uint4*>(plans + tile);
+#pragma unroll
+    for (int q = 0; q < 4; q++) dst[q] = src[q];
+}
+
+// thread 0 of a CTA: read the tile's plan, publish the staging bases, issue the copies.
+// arrays[k] / smem[k] / elem_bytes[k]: the SoA streams to stage (1 for density, 3 for force).
+template <int NARR>
+__device__ __forceinline__ void stage_from_plan(const TilePlan* __restrict__ tp, const void* const (&arrays)[NARR],
+                                                void* const (&smem)[NARR], const uint32_t (&elem_bytes)[NARR], uint64_t* bar,
+                                                SpanPlan* plan) {
+    constexpr int NI = SPH_MAX_ROWS * 3;
+    const uint4* src = reinterpret_cast<const uint4*>(tp);
+    const uint4 w0 = __ldg(src), w1 = __ldg(src + 1), w2 = __ldg(src + 2), w3 = __ldg(src + 3);
+    const uint32_t lo[NI] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y};
+    const uint32_t len[NI] = {w1.z, w1.w, w2.x, w2.y, w2.z, w2.w};
+    static_assert(NI == 6, "TilePlan word layout");
+    plan->row_first = w3.x;
+    const uint32_t flags = w3.y;
+    if (!(flags & 1u)) {
         plan->staged = 0;
         return;
     }
     plan->staged = 1;
+    uint32_t total = 0, off[NI];
 #pragma unroll
-    for (int t = 0; t < NI; t++) plan->base[t] = grouped ? (int)lo[t] - (int)off[t] : (int)lo[0];
+    for (int t = 0; t < NI; t++) { off[t] = total; total += len[t]; }
+#pragma unroll
+    for (int t = 0; t < NI; t++) plan->base[t] = (flags & 2u) ? (int)lo[t] - (int)off[t] : (int)lo[0];
     uint32_t bytes = 0;
 #pragma unroll
     for (int k = 0; k < NARR; k++) bytes += total * elem_bytes[k];
     mbar_arrive_expect_tx(bar, bytes);
 #pragma unroll
     for (int t = 0; t < NI; t++) {
-        const uint32_t len = hi[t] - lo[t];
-        if (len == 0) continue;
+        if (len[t] == 0) continue;
 #pragma unroll
         for (int k = 0; k < NARR; k++) {
             bulk_g2s(reinterpret_cast<char*>(smem[k]) + (size_t)off[t] * elem_bytes[k],
-                     reinterpret_cast<const char*>(arrays[k]) + (size_t)lo[t] * elem_bytes[k], len * elem_bytes[k], bar);
+                     reinterpret_cast<const char*>(arrays[k]) + (size_t)lo[t] * elem_bytes[k], len[t] * elem_bytes[k], bar);
         }
     }
 }
@@ -244,7 +282,8 @@ __device__ __forceinline__ float density_walk_staged(const DevParams& p, uint32_
 __global__ void __launch_bounds__(SPH_THREADS)
 k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* __restrict__ keys,
           const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk, float* __restrict__ rho,
-          uint32_t* __restrict__ wild_stamp /* null: slab mode */, const uint32_t* __restrict__ frame_time) {
+          uint32_t* __restrict__ wild_stamp /* null: slab mode */, const uint32_t* __restrict__ frame_time,
+          const TilePlan* __restrict__ plans) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP + 2];  // + pad: the pair loop may load one record past a span
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
@@ -257,7 +296,7 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
         const void* const arrays[1] = {pred_s};
         void* const smem[1] = {s_pred};
         const uint32_t eb[1] = {8u};
-        plan_and_stage<1>(p, i0, i1, keys, lb, arrays, smem, eb, &s_bar, &s_plan);
+        stage_from_plan<1>(plans + blockIdx.x, arrays, smem, eb, &s_bar, &s_plan);
     }
     const uint32_t i = i0 + threadIdx.x;
     const bool valid = i < p.own_begin + p.n;
@@ -726,6 +765,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
                   const float2* __restrict__ force_field, const uint32_t* __restrict__ frame_time,
                   const uint32_t* __restrict__ global_offset_dev /* slab mode with device-resolved metadata, else null */,
                   const uint32_t* __restrict__ wild_stamp /* null: always take the per-pair range tests */,
+                  const TilePlan* __restrict__ plans,
                   float2* __restrict__ pos_out, float2* __restrict__ vel_out, float2* __restrict__ dbg_accel,
                   float2* __restrict__ dbg_abs) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP];
@@ -743,7 +783,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
         const void* const arrays[3] = {pred_s, vel_s, rho};
         void* const smem[3] = {s_pred, s_vel, s_rho};
         const uint32_t eb[3] = {8u, 8u, 4u};
-        plan_and_stage<3>(p, i0, i1, keys, lb, arrays, smem, eb, &s_bar, &s_plan);
+        stage_from_plan<3>(plans + blockIdx.x, arrays, smem, eb, &s_bar, &s_plan);
     }
     const uint32_t i = i0 + threadIdx.x;
     const bool valid = i < p.own_begin + p.n;

@@ -33,6 +33,7 @@ struct Sim {
     uint32_t *idx_a = nullptr, *idx_b = nullptr;
     uint32_t *keys_sorted = nullptr, *idx_sorted = nullptr;            // aliases into the above
     uint32_t* sort_scratch = nullptr;
+    void* tile_plans = nullptr;         // TilePlan per tile of SPH_THREADS sorted particles (kernels_sph.cuh), 64 B each
     size_t sort_scratch_words = 0;
     uint32_t max_tiles = 0;
 

@@ -240,7 +240,9 @@ int fluid_slab_cells_density(FluidSim* h, uint32_t halo_below, uint32_t halo_abo
     s->launches++;
     s->mark("cells");
     if (s->n) {
-        k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho, nullptr, nullptr);
+        launch_tile_plans(s, p, s->keys_ext);
+        k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho, nullptr, nullptr,
+                                                                                         reinterpret_cast<const TilePlan*>(s->tile_plans));
         s->launches++;
     }
     s->mark("density");
@@ -274,7 +276,9 @@ int fluid_slab_cells_density_dev(FluidSim* h, const uint32_t* allmeta_dev) {
     s->launches += 4;
     s->mark("cells");
     if (s->n) {
-        k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho, nullptr, nullptr);
+        launch_tile_plans(s, p, s->keys_ext);
+        k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho, nullptr, nullptr,
+                                                                                         reinterpret_cast<const TilePlan*>(s->tile_plans));
         s->launches++;
     }
     s->mark("density");
