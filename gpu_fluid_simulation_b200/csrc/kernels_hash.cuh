@@ -12,12 +12,34 @@ namespace fluid {
 
 constexpr int HASH_THREADS = 256;
 
-// warp-aggregated shared-memory histogram update: neighbouring particles are in neighbouring cells
-// (the array is in last tick's key order), so lanes collide heavily on the upper digits.
+// warp-aggregated shared-memory histogram update. The array is in last tick's key order, so along the lanes of a warp
+// the digits come in runs: the first lane of every run adds the run's length (one shuffle and one vote instead of a
+// match_any, which kept the XU pipe at 39 % and led the stall samples in round 1). Any digit order is counted correctly;
+// unsorted input just makes the runs short.
 __device__ __forceinline__ void hist_add(uint32_t* s_hist, uint32_t digit, bool valid) {
-    uint32_t d = valid ? digit : 0xffffffffu;
-    uint32_t peers = __match_any_sync(0xffffffffu, d);
-    if (valid && (int)lane_id() == __ffs(peers) - 1) atomicAdd(s_hist + digit, (uint32_t)__popc(peers));
+    const uint32_t lane = lane_id();
+    const uint32_t d = valid ? digit : 0xffffffffu;
+    const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
+    const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0u || d != prev);
+    if (valid && ((heads >> lane) & 1u)) {
+        const uint32_t above = heads & ~((2u << lane) - 1u);  // run heads in the lanes above this one
+        const uint32_t next = above ? (uint32_t)__ffs(above) - 1u : 32u;
+        atomicAdd(s_hist + digit, next - lane);
+    }
+}
+
+// the two particles of every lane at once, for the upper digits: the array is in last tick's key order, so a warp's 64
+// keys nearly always share them — one vote and one atomic per warp; match_any only when they differ
+__device__ __forceinline__ void hist_add_pair_upper(uint32_t* s_hist, uint32_t d0, uint32_t d1, bool v0, bool v1) {
+    const uint32_t ref = __shfl_sync(0xffffffffu, d0, 0);  // lane 0's first particle is valid whenever any lane's is
+    const bool same = (!v0 || d0 == ref) && (!v1 || d1 == ref);
+    if (__all_sync(0xffffffffu, same)) {
+        const uint32_t cnt = __popc(__ballot_sync(0xffffffffu, v0)) + __popc(__ballot_sync(0xffffffffu, v1));
+        if (lane_id() == 0 && cnt) atomicAdd(s_hist + ref, cnt);
+    } else {
+        hist_add(s_hist, d0, v0);
+        hist_add(s_hist, d1, v1);
+    }
 }
 
 template <int PASSES>
@@ -52,8 +74,13 @@ k_predict_key_hist(const DevParams p, const float2* __restrict__ pos, const floa
         }
 #pragma unroll
         for (int q = 0; q < PASSES; q++) {
-            hist_add(s_hist + q * RADIX, (k0 >> (q * RADIX_BITS)) & (RADIX - 1), v0);
-            hist_add(s_hist + q * RADIX, (k1 >> (q * RADIX_BITS)) & (RADIX - 1), v1);
+            const uint32_t d0 = (k0 >> (q * RADIX_BITS)) & (RADIX - 1), d1 = (k1 >> (q * RADIX_BITS)) & (RADIX - 1);
+            if (q == 0) {
+                hist_add(s_hist, d0, v0);
+                hist_add(s_hist, d1, v1);
+            } else {
+                hist_add_pair_upper(s_hist + q * RADIX, d0, d1, v0, v1);
+            }
         }
     }
     __syncthreads();
