@@ -205,7 +205,7 @@ void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, 
 #define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                     \
     k_force_integrate<DBG, EX><<<blocks, SPH_THREADS, 0, s->stream>>>(p, s->pos_s, s->pred_s, s->vel_s, s->rho, keys,   \
                                                                       s->cell_lb, s->quirk, s->force_field,             \
-                                                                      s->d_frame_time, s->slab_goff_dev, s->slab ? nullptr : s->quirk + 2,      \
+                                                                      s->d_frame_time, s->slab_goff_dev, s->quirk + 2,      \
                                                                       reinterpret_cast<const TilePlan*>(s->tile_plans),                 \
                                                                       pos_out, vel_out, da, db)
     if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }

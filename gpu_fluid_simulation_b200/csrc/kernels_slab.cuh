@@ -74,27 +74,54 @@ k_slab_key_hist(const DevParams p, const float2* __restrict__ pos, const float2*
 __global__ void __launch_bounds__(GATHER_THREADS)
 k_slab_gather(const DevParams p, const uint32_t* __restrict__ sorted_keys, const uint32_t* __restrict__ sorted_idx,
               const float2* __restrict__ pos_in, const float2* __restrict__ vel_in, float2* __restrict__ pos_s,
-              float2* __restrict__ pred_s, float2* __restrict__ vel_s, uint32_t* __restrict__ keys_ext) {
+              float2* __restrict__ pred_s, float2* __restrict__ vel_s, uint32_t* __restrict__ keys_ext,
+              uint32_t* __restrict__ wild_stamp, const uint32_t* __restrict__ frame_time) {
     const uint32_t i = blockIdx.x * GATHER_THREADS + threadIdx.x;
     if (i >= p.n) return;
     const uint32_t src = __ldg(sorted_idx + i);
     const float2 ps = __ldg(pos_in + src), vs = __ldg(vel_in + src);
     const uint32_t o = p.own_begin + i;
+    const float2 pr = predict_position(p, ps, vs);
     pos_s[o] = ps;
     vel_s[o] = vs;
-    pred_s[o] = predict_position(p, ps, vs);
+    pred_s[o] = pr;
     keys_ext[o] = __ldg(sorted_keys + i);
+    // wild stamp of this tick (common.cuh tame_component); halo rows are tested where their keys are made
+    if (!(tame_component(pr.x) && tame_component(pr.y) && tame_component(vs.x) && tame_component(vs.y))) *wild_stamp = __ldg(frame_time);
+}
+__device__ __forceinline__ void stamp_if_wild(float2 pr, float2 vs, uint32_t* wild_stamp, const uint32_t* frame_time) {
+    if (!(tame_component(pr.x) && tame_component(pr.y) && tame_component(vs.x) && tame_component(vs.y))) *wild_stamp = __ldg(frame_time);
 }
 
 // keys of received halo particles from their predicted positions (same arithmetic as the hash pass)
 __global__ void k_slab_halo_keys(const DevParams p, const float2* __restrict__ pred_s, uint32_t* __restrict__ keys_ext,
-                                 uint32_t below_begin, uint32_t below_count, uint32_t above_begin, uint32_t above_count) {
+                                 uint32_t below_begin, uint32_t below_count, uint32_t above_begin, uint32_t above_count,
+                                 const float2* __restrict__ vel_s, uint32_t* __restrict__ wild_stamp,
+                                 const uint32_t* __restrict__ frame_time) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t i;
     if (t < below_count) i = below_begin + t;
     else if (t < below_count + above_count) i = above_begin + (t - below_count);
     else return;
-    keys_ext[i] = cell_key(p, __ldg(pred_s + i));
+    const float2 pr = __ldg(pred_s + i);
+    keys_ext[i] = cell_key(p, pr);
+    stamp_if_wild(pr, __ldg(vel_s + i), wild_stamp, frame_time);
+}
+
+// densities of the received halo rows (exchanged after the density pass): the last input of the force pass's stamp
+__global__ void k_slab_check_rho_halo(const float* __restrict__ rho, uint32_t below_begin, uint32_t below_count, uint32_t above_begin,
+                                      uint32_t above_count, const uint32_t* __restrict__ dyn_hb_ha /* {hb, ha} or null */,
+                                      uint32_t own_begin, uint32_t* __restrict__ wild_stamp, const uint32_t* __restrict__ frame_time) {
+    if (dyn_hb_ha) {  // device-resolved protocol: the counts live on the device, the windows are pad-sized
+        below_count = dyn_hb_ha[0]; above_count = dyn_hb_ha[1];
+        below_begin = own_begin - below_count;
+    }
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t i;
+    if (t < below_count) i = below_begin + t;
+    else if (t < below_count + above_count) i = above_begin + (t - below_count);
+    else return;
+    if (!(__ldg(rho + i) <= DIV_DEN_HI)) *wild_stamp = __ldg(frame_time);
 }
 
 // ---- device-resolved protocol: what the host used to read back between the sort and the cell tables --------------
@@ -135,7 +162,9 @@ __global__ void k_slab_resolve(const uint32_t* __restrict__ allmeta, int world, 
 }
 // keys of the received halo particles; grid over 2 * pad threads, counts from SlabDyn
 __global__ void k_slab_halo_keys_dev(const DevParams p, const float2* __restrict__ pred_s, uint32_t* __restrict__ keys_ext,
-                                     const SlabDyn* __restrict__ dyn, uint32_t own_begin, uint32_t n, uint32_t pad) {
+                                     const SlabDyn* __restrict__ dyn, uint32_t own_begin, uint32_t n, uint32_t pad,
+                                     const float2* __restrict__ vel_s, uint32_t* __restrict__ wild_stamp,
+                                     const uint32_t* __restrict__ frame_time) {
     const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     uint32_t i;
     if (t < pad) {
@@ -145,7 +174,9 @@ __global__ void k_slab_halo_keys_dev(const DevParams p, const float2* __restrict
         if (t - pad >= dyn->ha) return;
         i = own_begin + n + (t - pad);
     } else return;
-    keys_ext[i] = cell_key(p, __ldg(pred_s + i));
+    const float2 pr = __ldg(pred_s + i);
+    keys_ext[i] = cell_key(p, pr);
+    stamp_if_wild(pr, __ldg(vel_s + i), wild_stamp, frame_time);
 }
 // an empty extended range still needs a valid (all-empty) table
 __global__ void k_slab_fill_if_empty(uint32_t* __restrict__ cell_lb, uint32_t first, uint32_t count, const SlabDyn* __restrict__ dyn) {

@@ -198,7 +198,8 @@ int fluid_slab_sort(FluidSim* h, uint32_t n_from_below, uint32_t n_from_above, u
     p.own_begin = s->sorted_off;
     if (s->n) {
         k_slab_gather<<<(s->n + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
-            p, s->keys_sorted, s->idx_sorted, s->pos_a + begin, s->vel_a + begin, s->pos_s, s->pred_s, s->vel_s, s->keys_ext);
+            p, s->keys_sorted, s->idx_sorted, s->pos_a + begin, s->vel_a + begin, s->pos_s, s->pred_s, s->vel_s, s->keys_ext,
+            s->quirk + 2, s->d_frame_time);
         s->launches++;
     }
     const uint32_t row_first = s->slab_rows.bounds[s->slab_rows.rank], row_end = s->slab_rows.bounds[s->slab_rows.rank + 1];
@@ -223,7 +224,7 @@ int fluid_slab_cells_density(FluidSim* h, uint32_t halo_below, uint32_t halo_abo
     const uint32_t halos = halo_below + halo_above;
     if (halos) {
         k_slab_halo_keys<<<(halos + 255) / 256, 256, 0, s->stream>>>(p, s->pred_s, s->keys_ext, p.ext_begin, halo_below,
-                                                                     s->sorted_off + s->n, halo_above);
+                                                                     s->sorted_off + s->n, halo_above, s->vel_s, s->quirk + 2, s->d_frame_time);
         s->launches++;
     }
     const uint32_t ext = p.ext_end - p.ext_begin;
@@ -241,7 +242,7 @@ int fluid_slab_cells_density(FluidSim* h, uint32_t halo_below, uint32_t halo_abo
     s->mark("cells");
     if (s->n) {
         launch_tile_plans(s, p, s->keys_ext);
-        k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho, nullptr, nullptr,
+        k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho, s->quirk + 2, s->d_frame_time,
                                                                                          reinterpret_cast<const TilePlan*>(s->tile_plans));
         s->launches++;
     }
@@ -264,7 +265,8 @@ int fluid_slab_cells_density_dev(FluidSim* h, const uint32_t* allmeta_dev) {
     s->slab_goff_dev = &dyn->global_offset;
     const uint32_t pad = s->slab_pad;
     k_slab_resolve<<<1, 32, 0, s->stream>>>(allmeta_dev, s->slab_rows.world, s->slab_rows.rank, s->sorted_off, s->n, pad, dyn, s->quirk);
-    k_slab_halo_keys_dev<<<(2u * pad + 255) / 256, 256, 0, s->stream>>>(p, s->pred_s, s->keys_ext, dyn, s->sorted_off, s->n, pad);
+    k_slab_halo_keys_dev<<<(2u * pad + 255) / 256, 256, 0, s->stream>>>(p, s->pred_s, s->keys_ext, dyn, s->sorted_off, s->n, pad, s->vel_s, s->quirk + 2,
+                                                                  s->d_frame_time);
     const uint32_t brow0 = s->slab_rows.bounds[s->slab_rows.rank], brow1 = s->slab_rows.bounds[s->slab_rows.rank + 1];
     const uint32_t fill_lo = (brow0 > 0 ? brow0 - 1u : 0u) * s->grid_w;
     const uint32_t fill_hi = (uint32_t)std::min<uint64_t>((uint64_t)(brow1 + 1u) * s->grid_w + 1u, (uint64_t)s->num_cells + 1u);
@@ -277,7 +279,7 @@ int fluid_slab_cells_density_dev(FluidSim* h, const uint32_t* allmeta_dev) {
     s->mark("cells");
     if (s->n) {
         launch_tile_plans(s, p, s->keys_ext);
-        k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho, nullptr, nullptr,
+        k_density<<<(s->n + SPH_THREADS - 1) / SPH_THREADS, SPH_THREADS, 0, s->stream>>>(p, s->pred_s, s->keys_ext, s->cell_lb, s->quirk, s->rho, s->quirk + 2, s->d_frame_time,
                                                                                          reinterpret_cast<const TilePlan*>(s->tile_plans));
         s->launches++;
     }
@@ -289,6 +291,18 @@ int fluid_slab_cells_density_dev(FluidSim* h, const uint32_t* allmeta_dev) {
 // phase 7b: force + integrate over the owned particles; the new state lands at state_off in key order
 int fluid_slab_force(FluidSim* h) {
     SLAB_OR_FAIL(h);
+    if (s->n) {
+        // densities of the halo rows arrived after the density pass: the last input of the tick's wild stamp
+        const DevParams& p = s->slab_params;
+        const bool dev = s->slab_goff_dev != nullptr;
+        const uint32_t hb = dev ? s->slab_pad : s->sorted_off - p.ext_begin, ha = dev ? s->slab_pad : p.ext_end - (s->sorted_off + s->n);
+        if (hb + ha) {
+            k_slab_check_rho_halo<<<(hb + ha + 255) / 256, 256, 0, s->stream>>>(
+                s->rho, p.ext_begin, hb, s->sorted_off + s->n, ha, dev ? reinterpret_cast<const uint32_t*>(s->slab_dyn) : nullptr,
+                s->sorted_off, s->quirk + 2, s->d_frame_time);
+            s->launches++;
+        }
+    }
     if (s->n) launch_force(s, s->slab_params, (s->n + SPH_THREADS - 1) / SPH_THREADS, s->pos_a + s->state_off, s->vel_a + s->state_off);
     s->mark("force+integrate");
     if (s->timing) { s->marks_per_tick = s->n_marks; s->timed_ticks++; }
