@@ -58,12 +58,19 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
-            self.t = threading.Thread(target=lambda: [self.lines.append(l) for l in self.proc.stdout], daemon=True)
+            self.t = threading.Thread(target=lambda: [self.lines.append((time.time(), l)) for l in self.proc.stdout], daemon=True)
             self.t.start()
+            t_end = time.time() + 3.0  # nvidia-smi needs a few hundred ms to print its first line
+            while not self.lines and time.time() < t_end:
+                time.sleep(0.02)
         except Exception:
             self.proc = None
 
-    def stop(self):
+    def mark(self):
+        """wall-clock mark: samples are attributed to the interval between two marks"""
+        return time.time()
+
+    def stop(self, t0=None, t1=None):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -71,7 +78,9 @@ class ClockSampler:
         self.t.join(timeout=2)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for l in self.lines:
+        for t, l in self.lines:
+            if t0 is not None and not (t0 <= t <= t1 + 0.12):  # a -lms 100 sample describes the 100 ms before it
+                continue
             parts = [x.strip() for x in l.split(",")]
             if len(parts) < 6:
                 continue
@@ -197,25 +206,37 @@ def main():
     stream = torch.cuda.ExternalStream(sim.stream, device=local_rank)
 
     # ---- device-resident throughput -------------------------------------------------------------
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     sim.tick_n(ts, args.warmup)
     sim.sync()
     launches0 = sim.launch_count
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     sim.enable_timing(True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
+    t_clk0 = sampler.mark()
     with torch.cuda.stream(stream):
         e0.record(stream)
         sim.tick_n(ts, args.steps)
         e1.record(stream)
     sim.sync()
     torch.cuda.synchronize()
+    t_clk1 = sampler.mark()
     ms = e0.elapsed_time(e1)
-    clocks = sampler.stop()
     phases = sim.last_timing()
-    sim.enable_timing(False)
     launches = sim.launch_count - launches0
+    clock_window = "timed region"
+    if t_clk1 - t_clk0 < 0.35:
+        clock_window = "timed region + the same load continued untimed to 0.45 s (the region is shorter than the 100 ms sampling period x 4)"
+        # the timed region is shorter than a few 100 ms sampling periods: keep the same load running (untimed) until
+        # the sampler has seen it, and report those samples (the state is advanced, nothing below depends on it)
+        while time.time() - t_clk0 < 0.45:
+            sim.tick_n(ts, max(1, args.steps // 4))
+            sim.sync()
+        t_clk1 = sampler.mark()
+    clocks = sampler.stop(t_clk0, t_clk1)
+    clocks["window"] = clock_window
+    sim.enable_timing(False)
     ms_per_step = ms / args.steps
     value = n * args.steps / (ms * 1e-3)
 
