@@ -282,9 +282,27 @@ def test_config3_full_step_1m_dambreak(fluid, oracle):
     assert stats["floats_bit_exact"], stats
 
 
+def test_16m_full_step_bit_exact(fluid, oracle):
+    """16M particles, two ticks, every field of every particle against the oracle (the 64M scene of bench.py is checked
+    the same way by scripts/verify_full_size.py; result of the last run: profiles/r1c_verify_64m.json)."""
+    s, ts, p = scenes.uniform_box(4000)
+    osim = oracle.OracleSim(s, p, sort_mode=oracle.SORT_COUNTING)  # stable counting sort == the stable radix order
+    with fluid.FluidSimulation.new(0, s) as sim:
+        sim.upload_particles(p)
+        del p
+        for _ in range(2):
+            sim.tick(ts)
+            osim.tick(ts)
+        got = sim.download_particles()
+        table = sim.download_start_indices()
+    for f in ("grid", "position", "predicted_position", "velocity", "density"):
+        assert np.array_equal(np.ascontiguousarray(got[f]).view(np.uint32), np.ascontiguousarray(osim.p[f]).view(np.uint32)), f
+    assert np.array_equal(table, osim.table)
+
+
 @pytest.mark.parametrize("n_side", [4000])
 def test_large_scene_properties(fluid, n_side):
-    """sizes the oracle cannot afford (16M here; 64M in bench.py --verify): size-independent properties."""
+    """size-independent properties of the sort / table / hash at 16M (no oracle involved)."""
     s, ts, p = scenes.uniform_box(n_side)
     with fluid.FluidSimulation.new(0, s) as sim:
         sim.upload_particles(p)
