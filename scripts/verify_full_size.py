@@ -4,7 +4,7 @@
 
     python scripts/verify_full_size.py [n_side=8000] [ticks=2]
 
-Prints one JSON line. The oracle is test infrastructure (see oracle/README); this script is a checker, not product code.
+Prints one JSON line. The oracle is test infrastructure (see the header of oracle/oracle.py); this script is a checker, not product code.
 """
 import json
 import os

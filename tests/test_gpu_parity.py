@@ -112,7 +112,7 @@ def test_all_particles_in_one_cell_and_exact_duplicates(fluid, oracle):
     assert stats["floats_bit_exact"], stats
 
 
-@pytest.mark.parametrize("wild", ["tiny_velocity", "tiny_offset", "huge_mass", "none"])
+@pytest.mark.parametrize("wild", ["tiny_velocity", "tiny_offset", "huge_mass", "huge_stiffness", "none"])
 def test_range_tested_path_for_wild_inputs(fluid, oracle, wild):
     """the force pass skips most per-pair range tests of its shared-reciprocal divisions when the tick's inputs are
     "tame" (components zero or in [2^-70, 2^99], densities <= 2^20: stamped by the gather and density passes). One wild
@@ -129,6 +129,8 @@ def test_range_tested_path_for_wild_inputs(fluid, oracle, wild):
         p["velocity"][2000:2002] = 0
     elif wild == "huge_mass":
         ts = TickSettings(**{**ts.__dict__, "mass": 3e8})  # densities above 2^20
+    elif wild == "huge_stiffness":
+        ts = TickSettings(**{**ts.__dict__, "pressure_constant": 1e21})  # the per-launch bound on the pressure numerators fails
     stats = _check(fluid, oracle, s, ts, p, n_ticks=2)
     assert stats["floats_bit_exact"], stats
 
