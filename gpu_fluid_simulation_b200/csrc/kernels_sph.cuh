@@ -26,7 +26,10 @@
 namespace fluid {
 
 constexpr int SPH_THREADS = 256;
-constexpr int SPH_CAP = 1536;  // staged particles per CTA (3 row spans of ~256+2 cells, rounded)
+#ifndef FLUID_SPH_CAP
+#define FLUID_SPH_CAP 1536
+#endif
+constexpr int SPH_CAP = FLUID_SPH_CAP;  // staged particles per CTA (3 row spans of ~256+2 cells, rounded)
 
 constexpr int SPH_MAX_ROWS = 2;  // CTA row groups that get their own three staged spans
 
@@ -598,7 +601,7 @@ __device__ __forceinline__ void force_walk_global(const DevParams& p, const floa
 // order. Visiting order, hence every fp32 sum, is unchanged. All shared accesses use explicit 32-bit
 // shared-window addresses so the loops carry no address arithmetic beyond one add.
 #ifndef FLUID_FORCE_LIST
-#define FLUID_FORCE_LIST 16
+#define FLUID_FORCE_LIST 20
 #endif
 #ifndef FLUID_FORCE_MIN_CTAS
 #define FLUID_FORCE_MIN_CTAS 4
