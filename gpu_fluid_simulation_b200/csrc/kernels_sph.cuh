@@ -572,6 +572,52 @@ __device__ __forceinline__ void force_pair2(const DevParams& p, const PairConsts
     }
 }
 
+// the "fast" body for two neighbours at once (FLUID_MATH_FAST: one MUFU.RSQ and one MUFU.RCP per neighbour, contraction
+// allowed, a few ulp per term; branch decisions as in the exact body). A coincident neighbour (r == 0: RNG direction)
+// goes through the scalar body.
+template <bool DEBUG>
+__device__ __forceinline__ void force_pair2_fast(const DevParams& p, const PairConsts& c, float dxA, float dyA, float dxB, float dyB,
+                                                 float2 nvA, float2 nvB, float ndA, float ndB, bool hasB, float vx, float vy,
+                                                 float pressure, uint32_t& rand_seed, ForceAcc& acc) {
+    const f32x2 dx = pk2(dxA, dxB), dy = pk2(dyA, dyB), nd = pk2(ndA, ndB);
+    const f32x2 dvx = sub2(pk2(nvA.x, nvB.x), bc2(vx)), dvy = sub2(pk2(nvA.y, nvB.y), bc2(vy));
+    const f32x2 sq = fma2(dx, dx, mul2(dy, dy));
+    const float sqA = lo2(sq), sqB = hi2(sq);
+    if (sqA == 0.0f || (hasB && sqB == 0.0f)) {
+        force_pair<DEBUG, false>(p, c, dxA, dyA, sqA, nvA, ndA, vx, vy, pressure, rand_seed, acc);
+        if (hasB) force_pair<DEBUG, false>(p, c, dxB, dyB, sqB, nvB, ndB, vx, vy, pressure, rand_seed, acc);
+        return;
+    }
+    const f32x2 ir = pk2(rsqrt_approx(sqA), rsqrt_approx(sqB));
+    const f32x2 ind = pk2(rcp_approx(ndA), rcp_approx(ndB));
+    const f32x2 dst = mul2(sq, ir);
+    const f32x2 dirx = mul2(dx, ir), diry = mul2(dy, ir);
+    const bool inA = lo2(dst) <= p.h, inB = hi2(dst) <= p.h;
+    const f32x2 np = mul2(bc2(p.pressure_constant), sub2(nd, bc2(p.rest_density)));
+    const f32x2 kraw = mul2(sub2(bc2(p.h), dst), bc2(-p.spiky));
+    const f32x2 k = pk2(inA ? lo2(kraw) : 0.0f, inB ? hi2(kraw) : 0.0f);
+    const f32x2 w = mul2(mul2(k, mul2(add2(bc2(pressure), np), bc2(0.5f))), ind);
+    const f32x2 tx2 = mul2(dirx, w), ty2 = mul2(diry, w);
+    const f32x2 r2 = mul2(dst, dst);
+    const f32x2 poly = sub2(fma2(bc2(0.5f * p.h), ir, fma2(r2, bc2(p.inv_h2), mul2(mul2(r2, dst), bc2(-p.inv_two_h3)))), bc2(1.0f));
+    const f32x2 kvraw = mul2(bc2(p.visc_k), poly);
+    const f32x2 kv = pk2(inA ? lo2(kvraw) : 0.0f, inB ? hi2(kvraw) : 0.0f);
+    const f32x2 wv = mul2(ind, kv);
+    const f32x2 ux2 = mul2(dvx, wv), uy2 = mul2(dvy, wv);
+    acc.px += lo2(tx2); acc.py += lo2(ty2); acc.vx += lo2(ux2); acc.vy += lo2(uy2);
+    if (DEBUG) {
+        acc.ax += fabsf(lo2(tx2)) + fabsf(lo2(ux2)) * p.visc_coef;
+        acc.ay += fabsf(lo2(ty2)) + fabsf(lo2(uy2)) * p.visc_coef;
+    }
+    if (hasB) {
+        acc.px += hi2(tx2); acc.py += hi2(ty2); acc.vx += hi2(ux2); acc.vy += hi2(uy2);
+        if (DEBUG) {
+            acc.ax += fabsf(hi2(tx2)) + fabsf(hi2(ux2)) * p.visc_coef;
+            acc.ay += fabsf(hi2(ty2)) + fabsf(hi2(uy2)) * p.visc_coef;
+        }
+    }
+}
+
 // fallback walk straight from global memory (CTAs whose neighbourhood does not fit the staging buffer)
 template <bool DEBUG, bool EXACT>
 __device__ __forceinline__ void force_walk_global(const DevParams& p, const float2* __restrict__ pred,
@@ -729,31 +775,21 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
         // ---- phase B: evaluate ----
         const uint32_t cnt_bytes = wr - list_addr;
         const uint32_t max_bytes = __reduce_max_sync(0xffffffffu, cnt_bytes);
-        if (EXACT) {
-            // two list entries per iteration (force_pair2); an odd list ends with B = A, dropped
-            for (uint32_t k = 0; k < max_bytes; k += SPH_THREADS * 4u) {
-                if (k < cnt_bytes) {
-                    const bool hasB = k + SPH_THREADS * 2u < cnt_bytes;
-                    const uint32_t eA = lds_u16(list_addr + k);
-                    const uint32_t eB = hasB ? lds_u16(list_addr + k + SPH_THREADS * 2u) : eA;
-                    const float2 qA = lds_f2(eA), qB = lds_f2(eB);
-                    const float2 nvA = lds_f2(eA + vel_delta), nvB = lds_f2(eB + vel_delta);
-                    const float ndA = lds_f((eA >> 1) + rho_base), ndB = lds_f((eB >> 1) + rho_base);
+        // two list entries per iteration (force_pair2 / force_pair2_fast); an odd list ends with B = A, dropped
+        for (uint32_t k = 0; k < max_bytes; k += SPH_THREADS * 4u) {
+            if (k < cnt_bytes) {
+                const bool hasB = k + SPH_THREADS * 2u < cnt_bytes;
+                const uint32_t eA = lds_u16(list_addr + k);
+                const uint32_t eB = hasB ? lds_u16(list_addr + k + SPH_THREADS * 2u) : eA;
+                const float2 qA = lds_f2(eA), qB = lds_f2(eB);
+                const float2 nvA = lds_f2(eA + vel_delta), nvB = lds_f2(eB + vel_delta);
+                const float ndA = lds_f((eA >> 1) + rho_base), ndB = lds_f((eB >> 1) + rho_base);
+                if (EXACT)
                     force_pair2<DEBUG>(p, pc, fsub(qA.x, px), fsub(qA.y, py), fsub(qB.x, px), fsub(qB.y, py), nvA, nvB, ndA, ndB,
                                        hasB, tame, vx, vy, pressure, rand_seed, acc);
-                }
-            }
-        } else {
-            for (uint32_t k = 0; k < max_bytes; k += SPH_THREADS * 2u) {
-                if (k < cnt_bytes) {
-                    const uint32_t e = lds_u16(list_addr + k);
-                    const float2 q = lds_f2(e);
-                    const float2 nv = lds_f2(e + vel_delta);
-                    const float nd = lds_f((e >> 1) + rho_base);
-                    const float dx = fsub(q.x, px), dy = fsub(q.y, py);
-                    const float sq = fadd(fmul(dx, dx), fmul(dy, dy));
-                    force_pair<DEBUG, EXACT>(p, pc, dx, dy, sq, nv, nd, vx, vy, pressure, rand_seed, acc);
-                }
+                else
+                    force_pair2_fast<DEBUG>(p, pc, fsub(qA.x, px), fsub(qA.y, py), fsub(qB.x, px), fsub(qB.y, py), nvA, nvB, ndA, ndB,
+                                            hasB, vx, vy, pressure, rand_seed, acc);
             }
         }
         __syncwarp();
