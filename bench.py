@@ -12,7 +12,8 @@ same 64M box is partitioned into y-slabs over the ranks (strong scaling), with N
 
 One JSON line is printed by rank 0. `value` is device-timed (CUDA events on the library's stream, inputs resident
 in HBM); `e2e` is measured through the public API with HOST buffers (pinned upload of the full particle state +
-tick + download of the full state every step). `roofline` is for the dominant kernel (force+integrate) with its
+tick + download of the full state every step; `e2e.frame_pattern` adds the reference's own per-frame pattern: state
+resident, force-field upload + tick + headless render downloaded). `roofline` is for the dominant kernel (force+integrate) with its
 duration measured live by the library's per-phase CUDA events inside the timed region. `cpu_baseline` times the
 CPU oracle (the restatement of the reference's WGSL; the reference itself cannot run here) on a bounded sample.
 """
@@ -281,6 +282,27 @@ def main():
                "steps": k, "ms_per_step": 1e3 * dt / k,
                "note": "upload_particles (pinned host AoS) + tick + download_particles (pinned host AoS) every step"}
         del host_in, host_out
+        # the reference's own per-frame call pattern, for comparison (extra key, NOT the contract's e2e): the particle
+        # state stays on the device as it does in the reference; per frame the host uploads the force field
+        # (queue.write_buffer, src/renderer.rs:498-502), calls tick with host TickSettings, and receives the frame
+        # (fluid_shader.wgsl at 960 x 540, src/renderer.rs:15, as a headless RGBA8 image in host memory).
+        from gpu_fluid_simulation_b200 import field as F
+        tw, th = s.texture_size
+        field_pinned = torch.zeros((th, tw, 2), dtype=torch.float32).pin_memory()
+        field_host = field_pinned.numpy()
+        inv = F.inverse_projection(s.size)
+        kf = max(3, k)
+        sim.upload_force_field(field_host); sim.tick(ts); F.render(sim, inv, 960, 540, want_f32=False, want_rgba8=True)
+        t0 = time.perf_counter()
+        for _ in range(kf):
+            sim.upload_force_field(field_host)
+            sim.tick(ts)
+            F.render(sim, inv, 960, 540, want_f32=False, want_rgba8=True)  # synchronises
+        dtf = time.perf_counter() - t0
+        e2e["frame_pattern"] = {"value": n * kf / dtf, "unit": "particle-steps/s", "ms_per_step": 1e3 * dtf / kf, "steps": kf,
+                                "h2d_bytes_per_step": int(field_host.nbytes) + 60, "d2h_bytes_per_step": 960 * 540 * 4,
+                                "note": "state resident (as in the reference); per step: force-field upload + tick + headless "
+                                        "960x540 render downloaded to the host"}
 
     cpu = None
     if not args.no_cpu_baseline:
