@@ -166,6 +166,8 @@ def main():
     ap.add_argument("--math", default="exact", choices=["exact", "fast"],
                     help="force-pass arithmetic: exact = IEEE-rounded reference order (bit-identical to the oracle); "
                          "fast = hardware rsqrt/rcp + FMA (<= 1e-5 parity, tests/test_gpu_parity.py)")
+    ap.add_argument("--sort", default="auto", choices=["auto", "radix", "counting"],
+                    help="key-order path of the single-GPU tick (include/fluid_b200.h FLUID_SORT_*): identical results")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--e2e-steps", type=int, default=3)
@@ -201,6 +203,7 @@ def main():
     n = s.particle_count
     sim = fluid.FluidSimulation.new(local_rank, s)
     sim.math_mode = 1 if args.math == "fast" else 0
+    sim.sort_mode = {"auto": 0, "radix": 1, "counting": 2}[args.sort]
     if p is not None:
         sim.upload_particles(p)
     sim.sync()
@@ -225,6 +228,7 @@ def main():
     t_clk1 = sampler.mark()
     ms = e0.elapsed_time(e1)
     phases = sim.last_timing()
+    sort_path = "counting" if sim.last_sort_path == 2 else "radix"
     launches = sim.launch_count - launches0
     clock_window = "timed region"
     if t_clk1 - t_clk0 < 0.35:
@@ -245,8 +249,11 @@ def main():
     dom = max(ph, key=ph.get)
     dom_ms = ph[dom]
     achieved = ALGO_BYTES[dom] * n / (dom_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": {"force+integrate": "k_force_integrate", "density": "k_density", "sort": "k_onesweep_pass",
-                                            "predict+key+hist": "k_predict_key_hist", "gather+cells": "k_gather_cells"}[dom],
+    kernel_of = {"force+integrate": "k_force_integrate", "density": "k_density", "sort": "k_onesweep_pass",
+                 "predict+key+hist": "k_predict_key_hist", "gather+cells": "k_gather_cells"}
+    if sort_path == "counting":  # kernels_count.cuh; the phase names and SURVEY's algorithmic bytes stay the same
+        kernel_of.update({"sort": "k_cell_slots", "predict+key+hist": "k_predict_key_count", "gather+cells": "k_rank_gather_cells"})
+    roofline = {"bound": "hbm", "kernel": kernel_of[dom],
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "peak_source": peak_src, "algorithmic_bytes_per_particle": ALGO_BYTES[dom], "kernel_ms": dom_ms,
                 "share_of_step": dom_ms / ms_per_step,
@@ -313,7 +320,7 @@ def main():
     line = {"metric": "particle-steps/sec", "value": value, "unit": "particle-steps/s", "n_gpus": 1, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "particles": n, "math": args.math,
+            "config": {"workload": args.workload, "particles": n, "math": args.math, "sort": args.sort, "sort_path": sort_path,
                        "l2": "inputs larger than L2 (no flush)" if n * 64 > 126e6 * 2 else "state fits L2; steps run back to back as in the real simulation loop (no flush)",
                        "parallelism": "1 GPU"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}

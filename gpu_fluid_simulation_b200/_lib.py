@@ -83,6 +83,9 @@ PROTOTYPES = {
     "fluid_sim_set_tick_count": (_i, [_P, _u32]),
     "fluid_sim_set_math_mode": (_i, [_P, _i]),
     "fluid_sim_get_math_mode": (_i, [_P]),
+    "fluid_sim_set_sort_mode": (_i, [_P, _i]),
+    "fluid_sim_get_sort_mode": (_i, [_P]),
+    "fluid_sim_last_sort_path": (_i, [_P]),
     "fluid_sim_tick_hash_sort_only": (_i, [_P, C.POINTER(TickSettingsC)]),
     "fluid_sim_particle_count": (_u32, [_P]),
     "fluid_sim_grid_w": (_u32, [_P]),

@@ -14,6 +14,7 @@
 
 #include "common.cuh"
 #include "kernels_cells.cuh"
+#include "kernels_count.cuh"
 #include "kernels_hash.cuh"
 #include "kernels_sph.cuh"
 #include "radix_sort.cuh"
@@ -215,12 +216,12 @@ void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, 
 }
 
 template <int PASSES>
-static void launch_hash(Sim* s, const DevParams& p, uint32_t* hist) {
+static void launch_hash(Sim* s, const DevParams& p, uint32_t* hist, uint32_t bump) {
     const uint32_t pairs = (p.n + 1) / 2;
     uint32_t blocks = (pairs + HASH_THREADS - 1) / HASH_THREADS;
     const uint32_t max_blocks = (uint32_t)s->num_sms * 8u;
     if (blocks > max_blocks) blocks = max_blocks;
-    k_predict_key_hist<PASSES><<<blocks, HASH_THREADS, 0, s->stream>>>(p, s->pos_a, s->vel_a, s->keys_u, hist, s->d_frame_time);
+    k_predict_key_hist<PASSES><<<blocks, HASH_THREADS, 0, s->stream>>>(p, s->pos_a, s->vel_a, s->keys_u, hist, s->d_frame_time, bump);
 }
 
 int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
@@ -230,50 +231,91 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     n_marks = 0;
     mark("begin");
 
-    const uint32_t passes = sort_passes;
-    const uint32_t tiles = (n + SORT_TILE - 1) / SORT_TILE;
-    uint32_t* hist = sort_scratch;
-    uint32_t* counters = sort_scratch + MAX_PASSES * RADIX;
-    uint32_t* status = counters + RADIX;
-    // one memset clears histograms, tile tickets and the look-back status words of the passes in use
-    FLUID_CUDA(cudaMemsetAsync(sort_scratch, 0, ((size_t)MAX_PASSES * RADIX + RADIX + (size_t)passes * tiles * RADIX) * 4, stream));
-
-    switch (passes) {
-        case 1: launch_hash<1>(this, p, hist); break;
-        case 2: launch_hash<2>(this, p, hist); break;
-        case 3: launch_hash<3>(this, p, hist); break;
-        default: launch_hash<4>(this, p, hist); break;
-    }
-    launches++;
-    mark("predict+key+hist");
-    k_scan_histograms<<<passes, RADIX, 0, stream>>>(hist);
-    launches++;
-
-    const size_t sort_smem = (size_t)SORT_TILE * 2 * sizeof(uint32_t);
-    const uint32_t* kin = keys_u;
-    const uint32_t* vin = nullptr;
-    uint32_t* kout = keys_b;
-    uint32_t* vout = idx_a;
-    for (uint32_t q = 0; q < passes; q++) {
-        if (q == 0)
-            k_onesweep_pass<SORT_ITEMS, true><<<tiles, SORT_THREADS, sort_smem, stream>>>(
-                kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, n, (int)(q * RADIX_BITS));
-        else
-            k_onesweep_pass<SORT_ITEMS, false><<<tiles, SORT_THREADS, sort_smem, stream>>>(
-                kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, n, (int)(q * RADIX_BITS));
-        launches++;
-        kin = kout; vin = vout;
-        kout = (kout == keys_b) ? keys_c : keys_b;
-        vout = (vout == idx_a) ? idx_b : idx_a;
-    }
-    keys_sorted = const_cast<uint32_t*>(kin);
-    idx_sorted = const_cast<uint32_t*>(vin);
-    mark("sort");
-
+    // ---- sort path of this tick (kernels_count.cuh): counting sort over the cells unless a cell is too crowded ----
     const uint32_t gblocks = (n + GATHER_THREADS - 1) / GATHER_THREADS;
-    k_gather_cells<<<gblocks, GATHER_THREADS, 0, stream>>>(p, keys_sorted, idx_sorted, pos_a, vel_a, pos_s, pred_s, vel_s,
-                                                         start_indices, cell_lb, quirk, d_frame_time);
-    launches++;
+    const bool counted = sort_mode != FLUID_SORT_RADIX;
+    bool counting = false;
+    if (counted) {
+        FLUID_CUDA(cudaMemsetAsync(cell_count, 0, (size_t)cell_tiles * CELL_SCAN_TILE * 4, stream));
+        const uint32_t pairs = (n + 1) / 2;
+        uint32_t blocks = (pairs + HASH_THREADS - 1) / HASH_THREADS;
+        const uint32_t max_blocks = (uint32_t)num_sms * 8u;
+        if (blocks > max_blocks) blocks = max_blocks;
+        k_predict_key_count<<<blocks, HASH_THREADS, 0, stream>>>(p, pos_a, vel_a, keys_u, cell_count, d_frame_time);
+        launches++;
+        mark("predict+key+hist");
+        k_cell_reduce<<<cell_tiles, CELL_SCAN_THREADS, 0, stream>>>(cell_count, cell_tile_sum, cell_tile_max);
+        k_cell_downsweep<<<cell_tiles, CELL_SCAN_THREADS, 0, stream>>>(cell_count, cell_lb, cell_tile_sum, cell_tile_max, cell_tiles,
+                                                                      cell_max_dev);
+        launches += 2;
+        if (sort_mode == FLUID_SORT_COUNTING) {
+            counting = true;
+        } else {
+            // the published maximum lags the stream by the ticks in flight; after an upload it is unknown: wait once
+            if (!cell_max_known) {
+                FLUID_CUDA(cudaStreamSynchronize(stream));
+                cell_max_known = true;
+            }
+            counting = *cell_max_host <= COUNT_SORT_MAX_CELL;
+        }
+    }
+    if (counting) {
+        k_cell_slots<<<gblocks, GATHER_THREADS, 0, stream>>>(n, p.num_cells, keys_u, cell_count, keys_b, idx_a);
+        launches++;
+        mark("sort");
+        k_rank_gather_cells<<<gblocks, GATHER_THREADS, 0, stream>>>(p, keys_b, idx_a, pos_a, vel_a, pos_s, pred_s, vel_s, idx_b,
+                                                                   start_indices, cell_lb, quirk, d_frame_time);
+        launches++;
+        keys_sorted = keys_b;
+        idx_sorted = idx_b;
+        last_sort_path = FLUID_SORT_COUNTING;
+    } else {
+        const uint32_t passes = sort_passes;
+        const uint32_t tiles = (n + SORT_TILE - 1) / SORT_TILE;
+        uint32_t* hist = sort_scratch;
+        uint32_t* counters = sort_scratch + MAX_PASSES * RADIX;
+        uint32_t* status = counters + RADIX;
+        // one memset clears histograms, tile tickets and the look-back status words of the passes in use
+        FLUID_CUDA(cudaMemsetAsync(sort_scratch, 0, ((size_t)MAX_PASSES * RADIX + RADIX + (size_t)passes * tiles * RADIX) * 4, stream));
+
+        const uint32_t bump = counted ? 0u : 1u;  // k_predict_key_count has already advanced frame_time
+        switch (passes) {
+            case 1: launch_hash<1>(this, p, hist, bump); break;
+            case 2: launch_hash<2>(this, p, hist, bump); break;
+            case 3: launch_hash<3>(this, p, hist, bump); break;
+            default: launch_hash<4>(this, p, hist, bump); break;
+        }
+        launches++;
+        if (!counted) mark("predict+key+hist");
+        k_scan_histograms<<<passes, RADIX, 0, stream>>>(hist);
+        launches++;
+
+        const size_t sort_smem = (size_t)SORT_TILE * 2 * sizeof(uint32_t);
+        const uint32_t* kin = keys_u;
+        const uint32_t* vin = nullptr;
+        uint32_t* kout = keys_b;
+        uint32_t* vout = idx_a;
+        for (uint32_t q = 0; q < passes; q++) {
+            if (q == 0)
+                k_onesweep_pass<SORT_ITEMS, true><<<tiles, SORT_THREADS, sort_smem, stream>>>(
+                    kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, n, (int)(q * RADIX_BITS));
+            else
+                k_onesweep_pass<SORT_ITEMS, false><<<tiles, SORT_THREADS, sort_smem, stream>>>(
+                    kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, n, (int)(q * RADIX_BITS));
+            launches++;
+            kin = kout; vin = vout;
+            kout = (kout == keys_b) ? keys_c : keys_b;
+            vout = (vout == idx_a) ? idx_b : idx_a;
+        }
+        keys_sorted = const_cast<uint32_t*>(kin);
+        idx_sorted = const_cast<uint32_t*>(vin);
+        mark("sort");
+
+        k_gather_cells<<<gblocks, GATHER_THREADS, 0, stream>>>(p, keys_sorted, idx_sorted, pos_a, vel_a, pos_s, pred_s, vel_s,
+                                                             start_indices, cell_lb, quirk, d_frame_time);
+        launches++;
+        last_sort_path = FLUID_SORT_RADIX;
+    }
     mark("gather+cells");
     if (hash_sort_only) {
         // state stays consistent for download: positions/velocities unchanged, in sorted order
@@ -348,14 +390,23 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
     if (cudaStreamCreateWithFlags(&sim->stream, cudaStreamNonBlocking) != cudaSuccess) return fail(cuda_fail(cudaGetLastError(), "cudaStreamCreate", __FILE__, __LINE__));
     if ((rc = sim->alloc(sim->n)) != FLUID_OK) return fail(rc);
     const size_t tex_len = (size_t)s->texture_size[0] * s->texture_size[1];
+    // cell tables padded to whole scan tiles (kernels_count.cuh); the pad of cell_lb includes entry [num_cells]
+    sim->cell_tiles = (uint32_t)(((size_t)sim->num_cells + 1 + CELL_SCAN_TILE - 1) / CELL_SCAN_TILE);
+    const size_t cells_padded = (size_t)sim->cell_tiles * CELL_SCAN_TILE;
     if (cudaMalloc(&sim->start_indices, (size_t)sim->num_cells * 4) != cudaSuccess ||
-        cudaMalloc(&sim->cell_lb, ((size_t)sim->num_cells + 1) * 4) != cudaSuccess ||
+        cudaMalloc(&sim->cell_lb, cells_padded * 4) != cudaSuccess ||
+        cudaMalloc(&sim->cell_count, cells_padded * 4) != cudaSuccess ||
+        cudaMalloc(&sim->cell_tile_sum, (size_t)sim->cell_tiles * 4) != cudaSuccess ||
+        cudaMalloc(&sim->cell_tile_max, (size_t)sim->cell_tiles * 4) != cudaSuccess ||
+        cudaHostAlloc((void**)&sim->cell_max_host, 4, cudaHostAllocMapped) != cudaSuccess ||
+        cudaHostGetDevicePointer((void**)&sim->cell_max_dev, (void*)sim->cell_max_host, 0) != cudaSuccess ||
         cudaMalloc(&sim->quirk, 16) != cudaSuccess || cudaMalloc(&sim->d_frame_time, 4) != cudaSuccess ||
         cudaMalloc(&sim->force_field, tex_len * 8) != cudaSuccess)
         return fail(cuda_fail(cudaGetLastError(), "cudaMalloc(tables)", __FILE__, __LINE__));
     // zero-initialised like wgpu's un-mapped buffers (src/simulation.rs:204-218)
     cudaMemsetAsync(sim->start_indices, 0, (size_t)sim->num_cells * 4, sim->stream);
-    cudaMemsetAsync(sim->cell_lb, 0, ((size_t)sim->num_cells + 1) * 4, sim->stream);
+    cudaMemsetAsync(sim->cell_lb, 0, cells_padded * 4, sim->stream);
+    *sim->cell_max_host = 0;
     cudaMemsetAsync(sim->quirk, 0, 16, sim->stream);
     cudaMemsetAsync(sim->d_frame_time, 0, 4, sim->stream);
     cudaMemsetAsync(sim->force_field, 0, tex_len * 8, sim->stream);
@@ -397,8 +448,9 @@ void fluid_sim_destroy(FluidSim* h) {
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
                     s->idx_b, s->sort_scratch, s->tile_plans, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
                     s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta,
-                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn};
+                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count, s->cell_tile_sum, s->cell_tile_max};
     for (void* b : bufs) if (b) cudaFree(b);
+    if (s->cell_max_host) cudaFreeHost((void*)s->cell_max_host);
     for (auto& row : s->mark_events) for (auto& e : row) if (e) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);
     cudaGetLastError();
@@ -476,6 +528,7 @@ int fluid_sim_upload_particles(FluidSim* h, const FluidParticle* src) {
     int rc = ensure_stage(s);
     if (rc != FLUID_OK) return rc;
     FLUID_CUDA(cudaMemcpyAsync(s->aos_stage, src, (size_t)s->n * sizeof(FluidParticle), cudaMemcpyHostToDevice, s->stream));
+    s->cell_max_known = false;
     if (s->n == 0) return FLUID_OK;
     k_aos_to_soa<<<(s->n + 255) / 256, 256, 0, s->stream>>>(s->aos_stage, s->n, s->pos_a + s->state_off, s->pred_s + s->sorted_off,
                                                           s->vel_a + s->state_off, s->rho + s->sorted_off, s->keys_view());
@@ -602,6 +655,17 @@ int fluid_sim_get_math_mode(const FluidSim* h) {
     return (h && !reinterpret_cast<const Sim*>(h)->exact_math) ? FLUID_MATH_FAST : FLUID_MATH_EXACT;
 }
 
+int fluid_sim_set_sort_mode(FluidSim* h, int mode) {
+    SIM_OR_FAIL(h);
+    if (mode != FLUID_SORT_AUTO && mode != FLUID_SORT_RADIX && mode != FLUID_SORT_COUNTING)
+        return invalid("fluid_sim_set_sort_mode: unknown mode");
+    s->sort_mode = mode;
+    s->cell_max_known = false;
+    return FLUID_OK;
+}
+int fluid_sim_get_sort_mode(const FluidSim* h) { return h ? reinterpret_cast<const Sim*>(h)->sort_mode : FLUID_SORT_AUTO; }
+int fluid_sim_last_sort_path(const FluidSim* h) { return h ? reinterpret_cast<const Sim*>(h)->last_sort_path : FLUID_SORT_RADIX; }
+
 int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
     SIM_OR_FAIL(h);
     NOT_SLAB(s);
@@ -628,6 +692,7 @@ int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
     FLUID_CUDA(cudaStreamSynchronize(s->stream));
     cudaFree(pa); cudaFree(va); cudaFree(pr); cudaFree(rh); cudaFree(ks);
     s->idx_sorted = nullptr;
+    s->cell_max_known = false;
     if (dbg) return fluid_sim_enable_debug_force(h, 1);
     return FLUID_OK;
 }
@@ -640,6 +705,7 @@ int fluid_sim_set_particle_count(FluidSim* h, uint32_t n) {
     }
     if (n < 2 || n > s->capacity) return invalid("fluid_sim_set_particle_count: need 2 <= n <= capacity");
     s->n = n;
+    s->cell_max_known = false;
     return FLUID_OK;
 }
 

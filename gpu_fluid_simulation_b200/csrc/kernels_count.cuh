@@ -1,0 +1,236 @@
+// kernels_count.cuh — the key sort as a counting sort over the cells (single-GPU tick, default path).
+//
+// Replaces, like radix_sort.cuh, the reference's bitonic network (sort.wgsl:27-51 dispatched S(S+1)/2 times,
+// src/simulation.rs:323-347,518-524) and feeds the same consumers: sorted keys, the source permutation, the dense
+// lower-bound table `cell_lb` and the reference-compatible `start_indices` (compute.wgsl:45-56).
+//
+// A key IS a cell id (funcs.wgsl:216-218), there are ~4 particles per cell and `cell_lb` — the exclusive prefix sum of
+// the per-cell particle counts — has to be built anyway. So instead of three 8-bit radix passes over (key, index):
+//   1. k_predict_key_count   predict + key (K1+K2, compute.wgsl:8-42) and count[key] += 1           (one RED per run)
+//   2. k_cell_reduce / k_cell_downsweep   cell_lb = exclusive scan of count; cursor = cell_lb; largest count -> host
+//   3. k_cell_slots          slot = cursor[key]++ : writes (key, source index) into the cell's block, in ARRIVAL order
+//   4. k_rank_gather_cells   puts each cell's block into source-index order (rank = entries of the cell with a
+//                            smaller index), which makes the result the STABLE sort — exactly the order the LSD radix
+//                            passes produce, so the float sums downstream do not change a bit — and moves the payload.
+// Traffic per particle: 20 + 12 + ~56 B against 20 + 44 + 60 B for hash + 3 onesweep passes + gather.
+// The atomics are cheap because the array enters a tick in the previous tick's key order: along the lanes of a warp
+// the keys come in runs, the head of a run issues one atomic for the whole run, and the lanes of one instruction
+// touch a handful of adjacent 32-byte sectors. Arbitrary input order (first tick after an upload) is still sorted
+// correctly, only with shorter runs.
+// Step 4 costs O(cell population) per particle. The host therefore watches the largest cell population (published
+// into pinned host memory by step 2, read without a sync one or more ticks later, or after a sync on the first tick
+// after an upload) and takes the radix passes instead while any cell holds more than COUNT_SORT_MAX_CELL particles.
+#pragma once
+#include "common.cuh"
+#include "kernels_cells.cuh"
+#include "kernels_hash.cuh"
+
+namespace fluid {
+
+constexpr int CELL_SCAN_THREADS = 256;
+constexpr int CELL_SCAN_ITEMS = 16;  // consecutive cells per thread (4 x uint4)
+constexpr uint32_t CELL_SCAN_TILE = CELL_SCAN_THREADS * CELL_SCAN_ITEMS;
+constexpr uint32_t COUNT_SORT_MAX_CELL = 64;
+
+// count[cell] += 1 for every valid lane; the first lane of every run of equal cells adds the run's length
+__device__ __forceinline__ void cell_count_add(uint32_t* __restrict__ count, uint32_t cell, bool valid) {
+    const uint32_t lane = lane_id();
+    const uint32_t d = valid ? cell : 0xffffffffu;
+    const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
+    const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0u || d != prev);
+    if (valid && ((heads >> lane) & 1u)) {
+        const uint32_t above = heads & ~((2u << lane) - 1u);  // run heads in the lanes above this one
+        const uint32_t next = above ? (uint32_t)__ffs(above) - 1u : 32u;
+        atomicAdd(count + cell, next - lane);
+    }
+}
+
+// K1+K2 as in k_predict_key_hist (same arithmetic, same bits), with the per-cell count in place of the digit histograms
+__global__ void __launch_bounds__(HASH_THREADS)
+k_predict_key_count(const DevParams p, const float2* __restrict__ pos, const float2* __restrict__ vel,
+                    uint32_t* __restrict__ keys, uint32_t* __restrict__ count, uint32_t* __restrict__ frame_time) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) *frame_time += 1u;  // reference: self.tick += 1 (src/simulation.rs:460)
+    const uint32_t n_pairs = (p.n + 1u) >> 1;
+    const float4* pos4 = reinterpret_cast<const float4*>(pos);
+    const float4* vel4 = reinterpret_cast<const float4*>(vel);
+    const uint32_t stride = gridDim.x * HASH_THREADS;
+    const float y_h = rcp_refined(p.h);
+    const uint32_t last_cell = p.num_cells - 1u;
+    const uint32_t n_iter_end = (n_pairs + 31u) & ~31u;  // whole warps take part in the votes
+    for (uint32_t i = blockIdx.x * HASH_THREADS + threadIdx.x; i < n_iter_end; i += stride) {
+        const bool v0 = i < n_pairs;
+        const bool v1 = v0 && (2u * i + 1u < p.n);
+        uint32_t k0 = 0, k1 = 0;
+        if (v0) {
+            float4 ps = __ldg(pos4 + i), vs = __ldg(vel4 + i);  // arrays are padded to an even length
+            const float2 q0 = predict_position(p, make_float2(ps.x, ps.y), make_float2(vs.x, vs.y));
+            const float2 q1 = predict_position(p, make_float2(ps.z, ps.w), make_float2(vs.z, vs.w));
+            if (p.key_fast_div) { k0 = cell_key_shared(p, q0, y_h); k1 = cell_key_shared(p, q1, y_h); }
+            else { k0 = cell_key(p, q0); k1 = cell_key(p, q1); }
+            if (v1) reinterpret_cast<uint2*>(keys)[i] = make_uint2(k0, k1);
+            else keys[2u * i] = k0;
+        }
+        cell_count_add(count, min(k0, last_cell), v0);
+        cell_count_add(count, min(k1, last_cell), v1);
+    }
+}
+
+__device__ __forceinline__ uint32_t block_sum_256(uint32_t v, uint32_t* s_tmp /*8*/) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane_id() == 0) s_tmp[threadIdx.x >> 5] = v;
+    __syncthreads();
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < CELL_SCAN_THREADS / 32; w++) t += s_tmp[w];
+    __syncthreads();
+    return t;
+}
+__device__ __forceinline__ uint32_t block_max_256(uint32_t v, uint32_t* s_tmp /*8*/) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if (lane_id() == 0) s_tmp[threadIdx.x >> 5] = v;
+    __syncthreads();
+    uint32_t t = 0;
+#pragma unroll
+    for (int w = 0; w < CELL_SCAN_THREADS / 32; w++) t = max(t, s_tmp[w]);
+    __syncthreads();
+    return t;
+}
+
+// per tile of CELL_SCAN_TILE cells: particle count and largest cell (the count array is zero-padded to whole tiles)
+__global__ void __launch_bounds__(CELL_SCAN_THREADS)
+k_cell_reduce(const uint32_t* __restrict__ count, uint32_t* __restrict__ tile_sum, uint32_t* __restrict__ tile_max) {
+    __shared__ uint32_t s_tmp[CELL_SCAN_THREADS / 32];
+    const uint4* src = reinterpret_cast<const uint4*>(count + (size_t)blockIdx.x * CELL_SCAN_TILE) + threadIdx.x * (CELL_SCAN_ITEMS / 4);
+    uint32_t sum = 0, mx = 0;
+#pragma unroll
+    for (int j = 0; j < CELL_SCAN_ITEMS / 4; j++) {
+        const uint4 v = __ldg(src + j);
+        sum += v.x + v.y + v.z + v.w;
+        mx = max(max(mx, max(v.x, v.y)), max(v.z, v.w));
+    }
+    sum = block_sum_256(sum, s_tmp);
+    mx = block_max_256(mx, s_tmp);
+    if (threadIdx.x == 0) { tile_sum[blockIdx.x] = sum; tile_max[blockIdx.x] = mx; }
+}
+
+// cell_lb[c] = particles in cells below c (exclusive scan), also left in the count array as the cell's write cursor.
+// Entries past the last cell of the padded arrays receive n, which is what cell_lb[num_cells] has to hold.
+// Tile 0 also publishes the largest cell population of the tick to the host (pinned, mapped memory).
+__global__ void __launch_bounds__(CELL_SCAN_THREADS)
+k_cell_downsweep(uint32_t* __restrict__ count_cursor, uint32_t* __restrict__ cell_lb, const uint32_t* __restrict__ tile_sum,
+                 const uint32_t* __restrict__ tile_max, uint32_t ntiles, volatile uint32_t* __restrict__ host_max) {
+    __shared__ uint32_t s_tmp[CELL_SCAN_THREADS / 32];
+    __shared__ uint32_t s_warp[CELL_SCAN_THREADS / 32];
+    uint32_t part = 0;
+    for (uint32_t b = threadIdx.x; b < blockIdx.x; b += CELL_SCAN_THREADS) part += __ldg(tile_sum + b);
+    const uint32_t tile_base = block_sum_256(part, s_tmp);
+    if (blockIdx.x == 0) {
+        uint32_t mx = 0;
+        for (uint32_t b = threadIdx.x; b < ntiles; b += CELL_SCAN_THREADS) mx = max(mx, __ldg(tile_max + b));
+        mx = block_max_256(mx, s_tmp);
+        if (threadIdx.x == 0) *host_max = mx;
+    }
+    const size_t first = (size_t)blockIdx.x * CELL_SCAN_TILE + (size_t)threadIdx.x * CELL_SCAN_ITEMS;
+    uint4* cc = reinterpret_cast<uint4*>(count_cursor + first);
+    uint4* lb = reinterpret_cast<uint4*>(cell_lb + first);
+    uint4 v[CELL_SCAN_ITEMS / 4];
+    uint32_t total = 0;
+#pragma unroll
+    for (int j = 0; j < CELL_SCAN_ITEMS / 4; j++) {
+        v[j] = cc[j];
+        total += v[j].x + v[j].y + v[j].z + v[j].w;
+    }
+    uint32_t incl = total;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane_id() >= (uint32_t)o) incl += t;
+    }
+    if (lane_id() == 31) s_warp[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    uint32_t run = tile_base + incl - total;
+    for (uint32_t w = 0; w < (threadIdx.x >> 5); w++) run += s_warp[w];
+#pragma unroll
+    for (int j = 0; j < CELL_SCAN_ITEMS / 4; j++) {
+        uint4 o;
+        o.x = run; run += v[j].x;
+        o.y = run; run += v[j].y;
+        o.z = run; run += v[j].z;
+        o.w = run; run += v[j].w;
+        cc[j] = o;
+        lb[j] = o;
+    }
+}
+
+// slot = cursor[cell]++, one atomic per run of equal cells along the lanes; the run's lanes take consecutive slots, so a
+// cell's block is a concatenation of runs that are each in source order (k_rank_gather_cells orders the runs)
+__global__ void __launch_bounds__(GATHER_THREADS)
+k_cell_slots(uint32_t n, uint32_t num_cells, const uint32_t* __restrict__ keys_u, uint32_t* __restrict__ cursor,
+             uint32_t* __restrict__ slot_keys, uint32_t* __restrict__ slot_idx) {
+    const uint32_t i = blockIdx.x * GATHER_THREADS + threadIdx.x;  // grid is a whole number of warps
+    const uint32_t lane = lane_id();
+    const bool valid = i < n;
+    const uint32_t k = valid ? __ldg(keys_u + i) : 0u;
+    const uint32_t kc = min(k, num_cells - 1u);
+    const uint32_t d = valid ? kc : 0xffffffffu;
+    const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
+    const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0u || d != prev);
+    const uint32_t upto = (2u << lane) - 1u;                   // lanes 0..lane
+    const uint32_t head = 31u - (uint32_t)__clz(heads & upto);  // lane 0 is always a head
+    uint32_t base = 0;
+    if (valid && head == lane) {
+        const uint32_t above = heads & ~upto;
+        const uint32_t next = above ? (uint32_t)__ffs(above) - 1u : 32u;
+        base = atomicAdd(cursor + kc, next - lane);
+    }
+    base = __shfl_sync(0xffffffffu, base, head);
+    if (valid) {
+        const uint32_t slot = base + (lane - head);
+        slot_keys[slot] = k;
+        slot_idx[slot] = i;
+    }
+}
+
+// One thread per slot: final position inside the cell's block = number of entries of the block with a smaller source
+// index (stable order); then the payload move and the tables of k_gather_cells (same rules, same bits):
+// start_indices[key] = i at the first particle of every cell except sorted index 0 (compute.wgsl:45-56), the quirk
+// words for the lowest occupied cell, the wild stamp. cell_lb is already complete (k_cell_downsweep).
+__global__ void __launch_bounds__(GATHER_THREADS)
+k_rank_gather_cells(const DevParams p, const uint32_t* __restrict__ slot_keys, const uint32_t* __restrict__ slot_idx,
+                    const float2* __restrict__ pos_in, const float2* __restrict__ vel_in,
+                    float2* __restrict__ pos_s, float2* __restrict__ pred_s, float2* __restrict__ vel_s,
+                    uint32_t* __restrict__ idx_sorted, uint32_t* __restrict__ start_indices,
+                    const uint32_t* __restrict__ cell_lb, uint32_t* __restrict__ quirk,
+                    const uint32_t* __restrict__ frame_time) {
+    const uint32_t q = blockIdx.x * GATHER_THREADS + threadIdx.x;
+    if (q >= p.n) return;
+    const uint32_t k = __ldg(slot_keys + q);
+    const uint32_t kc = min(k, p.num_cells - 1u);
+    const uint32_t lo = __ldg(cell_lb + kc), hi = __ldg(cell_lb + kc + 1u);
+    const uint32_t src = __ldg(slot_idx + q);
+    uint32_t rank = 0;
+    for (uint32_t j = lo; j < hi; j++) rank += (__ldg(slot_idx + j) < src) ? 1u : 0u;
+    const uint32_t i = lo + rank;
+
+    const float2 ps = __ldg(pos_in + src);
+    const float2 vs = __ldg(vel_in + src);
+    pos_s[i] = ps;
+    vel_s[i] = vs;
+    const float2 pr = predict_position(p, ps, vs);  // same inputs, same ops as the key pass: same bits
+    pred_s[i] = pr;
+    idx_sorted[i] = src;
+    if (!(tame_component(pr.x) && tame_component(pr.y) && tame_component(vs.x) && tame_component(vs.y)))
+        quirk[2] = __ldg(frame_time);
+    if (rank == 0u) {
+        if (i == 0u) {
+            quirk[0] = kc;
+            quirk[1] = start_indices[kc];  // stale entry: nobody writes start_indices[key[0]] this tick
+        } else {
+            start_indices[kc] = i;  // compute.wgsl:52-54
+        }
+    }
+}
+
+}  // namespace fluid

@@ -45,11 +45,12 @@ __device__ __forceinline__ void hist_add_pair_upper(uint32_t* s_hist, uint32_t d
 template <int PASSES>
 __global__ void __launch_bounds__(HASH_THREADS)
 k_predict_key_hist(const DevParams p, const float2* __restrict__ pos, const float2* __restrict__ vel,
-                   uint32_t* __restrict__ keys, uint32_t* __restrict__ g_hist, uint32_t* __restrict__ frame_time) {
+                   uint32_t* __restrict__ keys, uint32_t* __restrict__ g_hist, uint32_t* __restrict__ frame_time,
+                   uint32_t bump /* 0 when k_predict_key_count already counted this tick */) {
     __shared__ uint32_t s_hist[PASSES * RADIX];
     for (int i = threadIdx.x; i < PASSES * RADIX; i += HASH_THREADS) s_hist[i] = 0;
     __syncthreads();
-    if (blockIdx.x == 0 && threadIdx.x == 0) *frame_time += 1u;  // reference: self.tick += 1 (src/simulation.rs:460)
+    if (blockIdx.x == 0 && threadIdx.x == 0) *frame_time += bump;  // reference: self.tick += 1 (src/simulation.rs:460)
 
     // two particles per thread per iteration: float4 loads of pos and vel, uint2 store of the keys
     const uint32_t n_pairs = (p.n + 1u) >> 1;

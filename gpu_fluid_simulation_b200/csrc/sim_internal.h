@@ -40,6 +40,16 @@ struct Sim {
     uint32_t* start_indices = nullptr;  // reference-compatible table (compute.wgsl:45-56), never cleared
     uint32_t* cell_lb = nullptr;        // dense lower-bound table, num_cells + 1 entries
     uint32_t* quirk = nullptr;          // [0] lowest occupied cell c0, [1] its stale start_indices entry
+
+    // counting sort over the cells (kernels_count.cuh): per-cell counts / write cursors, zero-padded to whole scan tiles
+    uint32_t* cell_count = nullptr;
+    uint32_t *cell_tile_sum = nullptr, *cell_tile_max = nullptr;
+    uint32_t cell_tiles = 0;
+    volatile uint32_t* cell_max_host = nullptr;  // pinned + mapped: largest cell population of the latest completed scan
+    uint32_t* cell_max_dev = nullptr;            // device alias of cell_max_host
+    bool cell_max_known = false;                 // false after anything that replaces the state (upload, resize)
+    int sort_mode = FLUID_SORT_AUTO;
+    int last_sort_path = FLUID_SORT_RADIX;       // what the most recently enqueued tick used
     uint32_t* d_frame_time = nullptr;   // device copy of `tick`, bumped by the first kernel of a tick
     float2* force_field = nullptr;      // reference `texture` (src/simulation.rs:213-218)
 

@@ -152,6 +152,21 @@ class FluidSimulation:
     def math_mode(self, mode: int):
         _lib.check(self._lib.fluid_sim_set_math_mode(self._h, int(mode)))
 
+    SORT_AUTO, SORT_RADIX, SORT_COUNTING = 0, 1, 2
+
+    @property
+    def sort_mode(self) -> int:
+        return int(self._lib.fluid_sim_get_sort_mode(self._h))
+
+    @sort_mode.setter
+    def sort_mode(self, mode: int):
+        _lib.check(self._lib.fluid_sim_set_sort_mode(self._h, int(mode)))
+
+    @property
+    def last_sort_path(self) -> int:
+        """SORT_RADIX or SORT_COUNTING: what the most recently enqueued tick used."""
+        return int(self._lib.fluid_sim_last_sort_path(self._h))
+
     def sync(self):
         _lib.check(self._lib.fluid_sim_sync(self._h))
 

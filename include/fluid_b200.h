@@ -144,6 +144,22 @@ int fluid_sim_set_tick_count(FluidSim* sim, uint32_t tick);
 int fluid_sim_set_math_mode(FluidSim* sim, int mode);
 int fluid_sim_get_math_mode(const FluidSim* sim);
 
+/* How the tick produces the key order (replaces sort.wgsl:27-51 + the schedule of src/simulation.rs:323-347 either way;
+ * both give the identical, stable order, so every downstream value is the same bit for bit).
+ * FLUID_SORT_COUNTING: counting sort over the cells (a key is a cell id, funcs.wgsl:216-218): per-cell counts, an
+ *   exclusive scan that IS the cell table, slot assignment, then each cell's few entries ranked by source index.
+ *   Cost grows with the square of a cell's population.
+ * FLUID_SORT_RADIX: onesweep LSD radix passes over (key, index); cost independent of the distribution.
+ * FLUID_SORT_AUTO (default): counting while the most crowded cell holds <= 64 particles (watched per tick without a
+ *   sync; one stream sync on the first tick after an upload), radix otherwise. Slab mode always uses the radix passes.
+ * fluid_sim_last_sort_path: which of the two the most recently enqueued tick used. */
+#define FLUID_SORT_AUTO 0
+#define FLUID_SORT_RADIX 1
+#define FLUID_SORT_COUNTING 2
+int fluid_sim_set_sort_mode(FluidSim* sim, int mode);
+int fluid_sim_get_sort_mode(const FluidSim* sim);
+int fluid_sim_last_sort_path(const FluidSim* sim);
+
 /* BASELINE.json config 2: spatial hash + key sort + cell-start table only
  * (reference passes K1..K4: compute.wgsl:8-56, sort.wgsl:27-51). Increments tick. */
 int fluid_sim_tick_hash_sort_only(FluidSim* sim, const FluidTickSettings* tick);

@@ -10,12 +10,14 @@ RTOL = 1e-5
 
 
 def run_pair(fluid, oracle, settings, tick_settings, particles, table=None, field=None, tick_count=0, n_ticks=1,
-             sort_mode=None, debug_force=True, math_mode=0):
+             sort_mode=None, debug_force=True, math_mode=0, gpu_sort_mode=None):
     """returns (oracle_sim, cuda_sim, extras) after n_ticks ticks from the same state."""
     O = oracle
     osim = O.OracleSim(settings, particles, sort_mode=O.SORT_STABLE if sort_mode is None else sort_mode)
     sim = fluid.FluidSimulation.new(0, settings)
     sim.math_mode = math_mode
+    if gpu_sort_mode is not None:
+        sim.sort_mode = gpu_sort_mode
     sim.upload_particles(particles)
     if table is not None:
         osim.table[:] = table
