@@ -260,14 +260,15 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
         }
     }
     if (counting) {
-        k_cell_slots<<<gblocks, GATHER_THREADS, 0, stream>>>(n, p.num_cells, keys_u, cell_count, keys_b, idx_a);
+        k_cell_slots<<<(n + GATHER_THREADS * SLOT_ITEMS - 1) / (GATHER_THREADS * SLOT_ITEMS), GATHER_THREADS, 0, stream>>>(
+            n, p.num_cells, keys_u, cell_count, keys_b, idx_a);
         launches++;
         mark("sort");
-        k_rank_gather_cells<<<gblocks, GATHER_THREADS, 0, stream>>>(p, keys_b, idx_a, pos_a, vel_a, pos_s, pred_s, vel_s, idx_b,
+        k_rank_gather_cells<<<(n + GATHER_THREADS * RANK_ITEMS - 1) / (GATHER_THREADS * RANK_ITEMS), GATHER_THREADS, 0, stream>>>(p, keys_b, idx_a, pos_a, vel_a, pos_s, pred_s, vel_s,
                                                                    start_indices, cell_lb, quirk, d_frame_time);
         launches++;
         keys_sorted = keys_b;
-        idx_sorted = idx_b;
+        idx_sorted = idx_b;  // filled on request: fluid_sim_download_permutation
         last_sort_path = FLUID_SORT_COUNTING;
     } else {
         const uint32_t passes = sort_passes;
@@ -584,6 +585,11 @@ int fluid_sim_download_permutation(FluidSim* h, uint32_t* dst) {
     SIM_OR_FAIL(h);
     if (!dst) return invalid("null destination");
     if (!s->idx_sorted) return invalid("fluid_sim_download_permutation: no tick has run yet");
+    if (!s->slab && s->last_sort_path == FLUID_SORT_COUNTING) {
+        k_rank_permutation<<<(s->n + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
+            s->n, s->num_cells, s->keys_b, s->idx_a, s->cell_lb, s->idx_b);
+        s->launches++;
+    }
     FLUID_CUDA(cudaMemcpyAsync(dst, s->idx_sorted, (size_t)s->n * 4, cudaMemcpyDeviceToHost, s->stream));
     FLUID_CUDA(cudaStreamSynchronize(s->stream));
     return FLUID_OK;

@@ -165,72 +165,135 @@ k_cell_downsweep(uint32_t* __restrict__ count_cursor, uint32_t* __restrict__ cel
 }
 
 // slot = cursor[cell]++, one atomic per run of equal cells along the lanes; the run's lanes take consecutive slots, so a
-// cell's block is a concatenation of runs that are each in source order (k_rank_gather_cells orders the runs)
+// cell's block is a concatenation of runs that are each in source order (k_rank_gather_cells orders the runs).
+// A warp takes SLOT_ITEMS rows of 32 consecutive particles and issues the rows' loads, then their atomics, back to back:
+// with one row per thread the kernel ran at the latency of the load -> atomic -> store chain (ncu: 0.33 ms at 64M for
+// 0.84 GB of traffic, full occupancy).
+#ifndef FLUID_SLOT_ITEMS
+#define FLUID_SLOT_ITEMS 4
+#endif
+constexpr int SLOT_ITEMS = FLUID_SLOT_ITEMS;
 __global__ void __launch_bounds__(GATHER_THREADS)
 k_cell_slots(uint32_t n, uint32_t num_cells, const uint32_t* __restrict__ keys_u, uint32_t* __restrict__ cursor,
              uint32_t* __restrict__ slot_keys, uint32_t* __restrict__ slot_idx) {
-    const uint32_t i = blockIdx.x * GATHER_THREADS + threadIdx.x;  // grid is a whole number of warps
     const uint32_t lane = lane_id();
-    const bool valid = i < n;
-    const uint32_t k = valid ? __ldg(keys_u + i) : 0u;
-    const uint32_t kc = min(k, num_cells - 1u);
-    const uint32_t d = valid ? kc : 0xffffffffu;
-    const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
-    const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0u || d != prev);
-    const uint32_t upto = (2u << lane) - 1u;                   // lanes 0..lane
-    const uint32_t head = 31u - (uint32_t)__clz(heads & upto);  // lane 0 is always a head
-    uint32_t base = 0;
-    if (valid && head == lane) {
-        const uint32_t above = heads & ~upto;
-        const uint32_t next = above ? (uint32_t)__ffs(above) - 1u : 32u;
-        base = atomicAdd(cursor + kc, next - lane);
+    const uint32_t warp = (blockIdx.x * GATHER_THREADS + threadIdx.x) >> 5;
+    const uint32_t first = warp * (32u * SLOT_ITEMS) + lane;
+    const uint32_t upto = (2u << lane) - 1u;  // lanes 0..lane
+    uint32_t k[SLOT_ITEMS], head[SLOT_ITEMS], base[SLOT_ITEMS];
+#pragma unroll
+    for (int j = 0; j < SLOT_ITEMS; j++) {
+        const uint32_t i = first + j * 32u;
+        k[j] = i < n ? __ldg(keys_u + i) : 0u;
     }
-    base = __shfl_sync(0xffffffffu, base, head);
-    if (valid) {
-        const uint32_t slot = base + (lane - head);
-        slot_keys[slot] = k;
-        slot_idx[slot] = i;
+#pragma unroll
+    for (int j = 0; j < SLOT_ITEMS; j++) {
+        const bool valid = first + j * 32u < n;
+        const uint32_t kc = min(k[j], num_cells - 1u);
+        const uint32_t d = valid ? kc : 0xffffffffu;
+        const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
+        const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0u || d != prev);
+        head[j] = 31u - (uint32_t)__clz(heads & upto);  // lane 0 is always a head
+        base[j] = 0;
+        if (valid && head[j] == lane) {
+            const uint32_t above = heads & ~upto;
+            const uint32_t next = above ? (uint32_t)__ffs(above) - 1u : 32u;
+            base[j] = atomicAdd(cursor + kc, next - lane);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < SLOT_ITEMS; j++) {
+        const uint32_t i = first + j * 32u;
+        const uint32_t b = __shfl_sync(0xffffffffu, base[j], head[j]);
+        if (i < n) {
+            const uint32_t slot = b + (lane - head[j]);
+            slot_keys[slot] = k[j];
+            slot_idx[slot] = i;
+        }
     }
 }
 
-// One thread per slot: final position inside the cell's block = number of entries of the block with a smaller source
-// index (stable order); then the payload move and the tables of k_gather_cells (same rules, same bits):
-// start_indices[key] = i at the first particle of every cell except sorted index 0 (compute.wgsl:45-56), the quirk
-// words for the lowest occupied cell, the wild stamp. cell_lb is already complete (k_cell_downsweep).
+// Per slot: final position inside the cell's block = number of entries of the block with a smaller source index (stable
+// order); then the payload move and the tables of k_gather_cells (same rules, same bits): start_indices[key] = i at the
+// first particle of every cell except sorted index 0 (compute.wgsl:45-56), the quirk words for the lowest occupied
+// cell, the wild stamp. cell_lb is already complete (k_cell_downsweep).
+// The pass is a chain of three dependent global loads ([key, index] -> [cell bounds, payload] -> [the block's indices])
+// and ran at exactly that latency with one slot per thread (0.66 ms at 64M, 4.8 TB/s); a thread therefore takes
+// RANK_ITEMS slots and the first RANK_UNROLL entries of a block are fetched as independent loads.
+#ifndef FLUID_RANK_ITEMS
+#define FLUID_RANK_ITEMS 2
+#endif
+constexpr int RANK_ITEMS = FLUID_RANK_ITEMS;
+constexpr int RANK_UNROLL = 8;
 __global__ void __launch_bounds__(GATHER_THREADS)
 k_rank_gather_cells(const DevParams p, const uint32_t* __restrict__ slot_keys, const uint32_t* __restrict__ slot_idx,
                     const float2* __restrict__ pos_in, const float2* __restrict__ vel_in,
                     float2* __restrict__ pos_s, float2* __restrict__ pred_s, float2* __restrict__ vel_s,
-                    uint32_t* __restrict__ idx_sorted, uint32_t* __restrict__ start_indices,
+                    uint32_t* __restrict__ start_indices,
                     const uint32_t* __restrict__ cell_lb, uint32_t* __restrict__ quirk,
                     const uint32_t* __restrict__ frame_time) {
+    const uint32_t q0 = blockIdx.x * (GATHER_THREADS * RANK_ITEMS) + threadIdx.x;
+    uint32_t kc[RANK_ITEMS], src[RANK_ITEMS], lo[RANK_ITEMS], hi[RANK_ITEMS], rank[RANK_ITEMS];
+    float2 ps[RANK_ITEMS], vs[RANK_ITEMS];
+#pragma unroll
+    for (int r = 0; r < RANK_ITEMS; r++) {
+        const uint32_t q = q0 + r * GATHER_THREADS;
+        const bool ok = q < p.n;  // a slot past the end reads particle 0 and cell 0 (the always-empty border cell) and stores nothing
+        kc[r] = ok ? min(__ldg(slot_keys + q), p.num_cells - 1u) : 0u;
+        src[r] = ok ? __ldg(slot_idx + q) : 0u;
+    }
+#pragma unroll
+    for (int r = 0; r < RANK_ITEMS; r++) {
+        lo[r] = __ldg(cell_lb + kc[r]);
+        hi[r] = __ldg(cell_lb + kc[r] + 1u);
+        ps[r] = __ldg(pos_in + src[r]);
+        vs[r] = __ldg(vel_in + src[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < RANK_ITEMS; r++) {
+        uint32_t v[RANK_UNROLL];
+#pragma unroll
+        for (int t = 0; t < RANK_UNROLL; t++) v[t] = (lo[r] + t < hi[r]) ? __ldg(slot_idx + lo[r] + t) : 0xffffffffu;
+        uint32_t c = 0;
+#pragma unroll
+        for (int t = 0; t < RANK_UNROLL; t++) c += (v[t] < src[r]) ? 1u : 0u;
+        rank[r] = c;
+    }
+#pragma unroll
+    for (int r = 0; r < RANK_ITEMS; r++) {
+        for (uint32_t j = lo[r] + RANK_UNROLL; j < hi[r]; j++) rank[r] += (__ldg(slot_idx + j) < src[r]) ? 1u : 0u;
+        if (q0 + r * GATHER_THREADS >= p.n) continue;
+        const uint32_t i = lo[r] + rank[r];
+        pos_s[i] = ps[r];
+        vel_s[i] = vs[r];
+        const float2 pr = predict_position(p, ps[r], vs[r]);  // same inputs, same ops as the key pass: same bits
+        pred_s[i] = pr;
+        if (!(tame_component(pr.x) && tame_component(pr.y) && tame_component(vs[r].x) && tame_component(vs[r].y)))
+            quirk[2] = __ldg(frame_time);
+        if (rank[r] == 0u) {
+            if (i == 0u) {
+                quirk[0] = kc[r];
+                quirk[1] = start_indices[kc[r]];  // stale entry: nobody writes start_indices[key[0]] this tick
+            } else {
+                start_indices[kc[r]] = i;  // compute.wgsl:52-54
+            }
+        }
+    }
+}
+
+// the source permutation (sorted index -> index before the tick) is a parity tap only: computed on request from the
+// slot arrays, which stay valid until the next tick (fluid_sim_download_permutation)
+__global__ void __launch_bounds__(GATHER_THREADS)
+k_rank_permutation(uint32_t n, uint32_t num_cells, const uint32_t* __restrict__ slot_keys, const uint32_t* __restrict__ slot_idx,
+                   const uint32_t* __restrict__ cell_lb, uint32_t* __restrict__ idx_sorted) {
     const uint32_t q = blockIdx.x * GATHER_THREADS + threadIdx.x;
-    if (q >= p.n) return;
-    const uint32_t k = __ldg(slot_keys + q);
-    const uint32_t kc = min(k, p.num_cells - 1u);
+    if (q >= n) return;
+    const uint32_t kc = min(__ldg(slot_keys + q), num_cells - 1u);
     const uint32_t lo = __ldg(cell_lb + kc), hi = __ldg(cell_lb + kc + 1u);
     const uint32_t src = __ldg(slot_idx + q);
     uint32_t rank = 0;
     for (uint32_t j = lo; j < hi; j++) rank += (__ldg(slot_idx + j) < src) ? 1u : 0u;
-    const uint32_t i = lo + rank;
-
-    const float2 ps = __ldg(pos_in + src);
-    const float2 vs = __ldg(vel_in + src);
-    pos_s[i] = ps;
-    vel_s[i] = vs;
-    const float2 pr = predict_position(p, ps, vs);  // same inputs, same ops as the key pass: same bits
-    pred_s[i] = pr;
-    idx_sorted[i] = src;
-    if (!(tame_component(pr.x) && tame_component(pr.y) && tame_component(vs.x) && tame_component(vs.y)))
-        quirk[2] = __ldg(frame_time);
-    if (rank == 0u) {
-        if (i == 0u) {
-            quirk[0] = kc;
-            quirk[1] = start_indices[kc];  // stale entry: nobody writes start_indices[key[0]] this tick
-        } else {
-            start_indices[kc] = i;  // compute.wgsl:52-54
-        }
-    }
+    idx_sorted[lo + rank] = src;
 }
 
 }  // namespace fluid
