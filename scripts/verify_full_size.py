@@ -48,6 +48,7 @@ def main():
             out["fields"][f"tick{t + 1}.start_indices"] = diff
             out["identical"] &= diff == 0
             del got
+        out["sort_path"] = {1: "radix", 2: "counting"}[sim.last_sort_path]
     print(json.dumps(out), flush=True)
     return 0 if out["identical"] else 1
 
