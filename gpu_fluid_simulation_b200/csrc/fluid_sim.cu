@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -191,24 +192,41 @@ void Sim::mark(const char* name) {
     n_marks++;
 }
 
+// Launch with programmatic stream serialization: the kernel's CTAs may become resident while the previous kernel of the
+// stream drains; every kernel launched this way starts with pdl_enter() (common.cuh), which waits for the previous grid
+// to complete before touching memory. `pdl == false` is a plain launch.
+template <typename... KArgs, typename... Args>
+static void launch_pdl(bool pdl, void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t stream, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // staging plans of the two neighbour passes (kernels_sph.cuh TilePlan), once per tick after the cell table is complete
-void launch_tile_plans(Sim* s, const DevParams& p, const uint32_t* keys) {
+void launch_tile_plans(Sim* s, const DevParams& p, const uint32_t* keys, bool pdl = false) {
     const uint32_t ntiles = (p.n + SPH_THREADS - 1) / SPH_THREADS;
     if (!ntiles) return;
-    k_tile_plans<<<(ntiles + 127) / 128, 128, 0, s->stream>>>(p, keys, s->cell_lb, ntiles, reinterpret_cast<TilePlan*>(s->tile_plans));
+    launch_pdl(pdl, k_tile_plans, dim3((ntiles + 127) / 128), dim3(128), s->stream, p, keys, s->cell_lb, ntiles,
+               reinterpret_cast<TilePlan*>(s->tile_plans));
     s->launches++;
 }
 
-void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, float2* vel_out) {
+void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, float2* vel_out, bool pdl = false) {
     float2* da = s->debug_force ? s->dbg_accel : nullptr;
     float2* db = s->debug_force ? s->dbg_abs : nullptr;
     const uint32_t* keys = s->slab ? s->keys_ext : s->keys_sorted;
 #define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                     \
-    k_force_integrate<DBG, EX><<<blocks, SPH_THREADS, 0, s->stream>>>(p, s->pos_s, s->pred_s, s->vel_s, s->rho, keys,   \
-                                                                      s->cell_lb, s->quirk, s->force_field,             \
-                                                                      s->d_frame_time, s->slab_goff_dev, s->quirk + 2,      \
-                                                                      reinterpret_cast<const TilePlan*>(s->tile_plans),                 \
-                                                                      pos_out, vel_out, da, db)
+    launch_pdl(pdl, k_force_integrate<DBG, EX>, dim3(blocks), dim3(SPH_THREADS), s->stream, p, s->pos_s, s->pred_s, s->vel_s, \
+               s->rho, keys, s->cell_lb, s->quirk, s->force_field, s->d_frame_time, s->slab_goff_dev, s->quirk + 2,     \
+               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db)
     if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
     else { if (s->exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
 #undef FLUID_LAUNCH_FORCE
@@ -236,17 +254,20 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     const bool counted = sort_mode != FLUID_SORT_RADIX;
     bool counting = false;
     if (counted) {
-        FLUID_CUDA(cudaMemsetAsync(cell_count, 0, (size_t)cell_tiles * CELL_SCAN_TILE * 4, stream));
+        // the two count arrays alternate: this tick's was cleared by the previous counted tick's scan (or at create)
+        cell_count = cell_count_buf[cell_count_cur];
+        uint32_t* const count_next = cell_count_buf[cell_count_cur ^ 1];
+        cell_count_cur ^= 1;
         const uint32_t pairs = (n + 1) / 2;
         uint32_t blocks = (pairs + HASH_THREADS - 1) / HASH_THREADS;
         const uint32_t max_blocks = (uint32_t)num_sms * 8u;
         if (blocks > max_blocks) blocks = max_blocks;
-        k_predict_key_count<<<blocks, HASH_THREADS, 0, stream>>>(p, pos_a, vel_a, keys_u, cell_count, d_frame_time);
+        launch_pdl(pdl, k_predict_key_count, dim3(blocks), dim3(HASH_THREADS), stream, p, pos_a, vel_a, keys_u, cell_count, d_frame_time);
         launches++;
         mark("predict+key+hist");
-        k_cell_reduce<<<cell_tiles, CELL_SCAN_THREADS, 0, stream>>>(cell_count, cell_tile_sum, cell_tile_max);
-        k_cell_downsweep<<<cell_tiles, CELL_SCAN_THREADS, 0, stream>>>(cell_count, cell_lb, cell_tile_sum, cell_tile_max, cell_tiles,
-                                                                      cell_max_dev);
+        launch_pdl(pdl, k_cell_reduce, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_tile_sum, cell_tile_max);
+        launch_pdl(pdl, k_cell_downsweep, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_lb, cell_tile_sum,
+                   cell_tile_max, cell_tiles, cell_max_dev, count_next);
         launches += 2;
         if (sort_mode == FLUID_SORT_COUNTING) {
             counting = true;
@@ -260,12 +281,13 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
         }
     }
     if (counting) {
-        k_cell_slots<<<(n + GATHER_THREADS * SLOT_ITEMS - 1) / (GATHER_THREADS * SLOT_ITEMS), GATHER_THREADS, 0, stream>>>(
-            n, p.num_cells, keys_u, cell_count, keys_b, idx_a);
+        launch_pdl(pdl, k_cell_slots, dim3((n + GATHER_THREADS * SLOT_ITEMS - 1) / (GATHER_THREADS * SLOT_ITEMS)), dim3(GATHER_THREADS),
+                   stream, n, p.num_cells, keys_u, cell_count, keys_b, idx_a);
         launches++;
         mark("sort");
-        k_rank_gather_cells<<<(n + GATHER_THREADS * RANK_ITEMS - 1) / (GATHER_THREADS * RANK_ITEMS), GATHER_THREADS, 0, stream>>>(p, keys_b, idx_a, pos_a, vel_a, pos_s, pred_s, vel_s,
-                                                                   start_indices, cell_lb, quirk, d_frame_time);
+        launch_pdl(pdl, k_rank_gather_cells, dim3((n + GATHER_THREADS * RANK_ITEMS - 1) / (GATHER_THREADS * RANK_ITEMS)),
+                   dim3(GATHER_THREADS), stream, p, keys_b, idx_a, pos_a, vel_a, pos_s, pred_s, vel_s, start_indices, cell_lb, quirk,
+                   d_frame_time, reinterpret_cast<TilePlan*>(tile_plans));
         launches++;
         keys_sorted = keys_b;
         idx_sorted = idx_b;  // filled on request: fluid_sim_download_permutation
@@ -328,12 +350,12 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
         return FLUID_OK;
     }
     const uint32_t sblocks = (n + SPH_THREADS - 1) / SPH_THREADS;
-    launch_tile_plans(this, p, keys_sorted);
-    k_density<<<sblocks, SPH_THREADS, 0, stream>>>(p, pred_s, keys_sorted, cell_lb, quirk, rho, quirk + 2, d_frame_time,
-                                                   reinterpret_cast<const TilePlan*>(tile_plans));
+    if (!counting) launch_tile_plans(this, p, keys_sorted, pdl);  // counting path: made by k_rank_gather_cells
+    launch_pdl(pdl, k_density, dim3(sblocks), dim3(SPH_THREADS), stream, p, pred_s, keys_sorted, cell_lb, quirk, rho, quirk + 2,
+               d_frame_time, reinterpret_cast<const TilePlan*>(tile_plans));
     launches++;
     mark("density");
-    launch_force(this, p, sblocks, pos_a, vel_a);
+    launch_force(this, p, sblocks, pos_a, vel_a, pdl);
     mark("force+integrate");
     if (timing) { marks_per_tick = n_marks; timed_ticks++; }
     FLUID_CUDA(cudaGetLastError());
@@ -396,7 +418,8 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
     const size_t cells_padded = (size_t)sim->cell_tiles * CELL_SCAN_TILE;
     if (cudaMalloc(&sim->start_indices, (size_t)sim->num_cells * 4) != cudaSuccess ||
         cudaMalloc(&sim->cell_lb, cells_padded * 4) != cudaSuccess ||
-        cudaMalloc(&sim->cell_count, cells_padded * 4) != cudaSuccess ||
+        cudaMalloc(&sim->cell_count_buf[0], cells_padded * 4) != cudaSuccess ||
+        cudaMalloc(&sim->cell_count_buf[1], cells_padded * 4) != cudaSuccess ||
         cudaMalloc(&sim->cell_tile_sum, (size_t)sim->cell_tiles * 4) != cudaSuccess ||
         cudaMalloc(&sim->cell_tile_max, (size_t)sim->cell_tiles * 4) != cudaSuccess ||
         cudaHostAlloc((void**)&sim->cell_max_host, 4, cudaHostAllocMapped) != cudaSuccess ||
@@ -407,7 +430,13 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
     // zero-initialised like wgpu's un-mapped buffers (src/simulation.rs:204-218)
     cudaMemsetAsync(sim->start_indices, 0, (size_t)sim->num_cells * 4, sim->stream);
     cudaMemsetAsync(sim->cell_lb, 0, cells_padded * 4, sim->stream);
+    cudaMemsetAsync(sim->cell_count_buf[0], 0, cells_padded * 4, sim->stream);
+    cudaMemsetAsync(sim->cell_count_buf[1], 0, cells_padded * 4, sim->stream);
     *sim->cell_max_host = 0;
+    {
+        const char* no_pdl = getenv("FLUID_NO_PDL");
+        sim->pdl = !(no_pdl && no_pdl[0] == '1');
+    }
     cudaMemsetAsync(sim->quirk, 0, 16, sim->stream);
     cudaMemsetAsync(sim->d_frame_time, 0, 4, sim->stream);
     cudaMemsetAsync(sim->force_field, 0, tex_len * 8, sim->stream);
@@ -449,7 +478,7 @@ void fluid_sim_destroy(FluidSim* h) {
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
                     s->idx_b, s->sort_scratch, s->tile_plans, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
                     s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta,
-                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count, s->cell_tile_sum, s->cell_tile_max};
+                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max};
     for (void* b : bufs) if (b) cudaFree(b);
     if (s->cell_max_host) cudaFreeHost((void*)s->cell_max_host);
     for (auto& row : s->mark_events) for (auto& e : row) if (e) cudaEventDestroy(e);
@@ -667,6 +696,10 @@ int fluid_sim_set_sort_mode(FluidSim* h, int mode) {
         return invalid("fluid_sim_set_sort_mode: unknown mode");
     s->sort_mode = mode;
     s->cell_max_known = false;
+    // both count arrays clean again, whatever ran before (ticks in FLUID_SORT_RADIX mode do not touch them)
+    const size_t bytes = (size_t)s->cell_tiles * CELL_SCAN_TILE * 4;
+    FLUID_CUDA(cudaMemsetAsync(s->cell_count_buf[0], 0, bytes, s->stream));
+    FLUID_CUDA(cudaMemsetAsync(s->cell_count_buf[1], 0, bytes, s->stream));
     return FLUID_OK;
 }
 int fluid_sim_get_sort_mode(const FluidSim* h) { return h ? reinterpret_cast<const Sim*>(h)->sort_mode : FLUID_SORT_AUTO; }

@@ -24,6 +24,7 @@
 #include "common.cuh"
 #include "kernels_cells.cuh"
 #include "kernels_hash.cuh"
+#include "kernels_sph.cuh"
 
 namespace fluid {
 
@@ -49,6 +50,7 @@ __device__ __forceinline__ void cell_count_add(uint32_t* __restrict__ count, uin
 __global__ void __launch_bounds__(HASH_THREADS)
 k_predict_key_count(const DevParams p, const float2* __restrict__ pos, const float2* __restrict__ vel,
                     uint32_t* __restrict__ keys, uint32_t* __restrict__ count, uint32_t* __restrict__ frame_time) {
+    pdl_enter();
     if (blockIdx.x == 0 && threadIdx.x == 0) *frame_time += 1u;  // reference: self.tick += 1 (src/simulation.rs:460)
     const uint32_t n_pairs = (p.n + 1u) >> 1;
     const float4* pos4 = reinterpret_cast<const float4*>(pos);
@@ -101,6 +103,7 @@ __device__ __forceinline__ uint32_t block_max_256(uint32_t v, uint32_t* s_tmp /*
 // per tile of CELL_SCAN_TILE cells: particle count and largest cell (the count array is zero-padded to whole tiles)
 __global__ void __launch_bounds__(CELL_SCAN_THREADS)
 k_cell_reduce(const uint32_t* __restrict__ count, uint32_t* __restrict__ tile_sum, uint32_t* __restrict__ tile_max) {
+    pdl_enter();
     __shared__ uint32_t s_tmp[CELL_SCAN_THREADS / 32];
     const uint4* src = reinterpret_cast<const uint4*>(count + (size_t)blockIdx.x * CELL_SCAN_TILE) + threadIdx.x * (CELL_SCAN_ITEMS / 4);
     uint32_t sum = 0, mx = 0;
@@ -118,9 +121,13 @@ k_cell_reduce(const uint32_t* __restrict__ count, uint32_t* __restrict__ tile_su
 // cell_lb[c] = particles in cells below c (exclusive scan), also left in the count array as the cell's write cursor.
 // Entries past the last cell of the padded arrays receive n, which is what cell_lb[num_cells] has to hold.
 // Tile 0 also publishes the largest cell population of the tick to the host (pinned, mapped memory).
+// `zero_next` is the count array of the NEXT tick (the two alternate): clearing it here, tile by tile, replaces a
+// per-tick memset, i.e. one stream operation between the force pass and the next tick's first kernel.
 __global__ void __launch_bounds__(CELL_SCAN_THREADS)
 k_cell_downsweep(uint32_t* __restrict__ count_cursor, uint32_t* __restrict__ cell_lb, const uint32_t* __restrict__ tile_sum,
-                 const uint32_t* __restrict__ tile_max, uint32_t ntiles, volatile uint32_t* __restrict__ host_max) {
+                 const uint32_t* __restrict__ tile_max, uint32_t ntiles, volatile uint32_t* __restrict__ host_max,
+                 uint32_t* __restrict__ zero_next) {
+    pdl_enter();
     __shared__ uint32_t s_tmp[CELL_SCAN_THREADS / 32];
     __shared__ uint32_t s_warp[CELL_SCAN_THREADS / 32];
     uint32_t part = 0;
@@ -135,6 +142,7 @@ k_cell_downsweep(uint32_t* __restrict__ count_cursor, uint32_t* __restrict__ cel
     const size_t first = (size_t)blockIdx.x * CELL_SCAN_TILE + (size_t)threadIdx.x * CELL_SCAN_ITEMS;
     uint4* cc = reinterpret_cast<uint4*>(count_cursor + first);
     uint4* lb = reinterpret_cast<uint4*>(cell_lb + first);
+    uint4* zn = reinterpret_cast<uint4*>(zero_next + first);
     uint4 v[CELL_SCAN_ITEMS / 4];
     uint32_t total = 0;
 #pragma unroll
@@ -161,6 +169,7 @@ k_cell_downsweep(uint32_t* __restrict__ count_cursor, uint32_t* __restrict__ cel
         o.w = run; run += v[j].w;
         cc[j] = o;
         lb[j] = o;
+        zn[j] = make_uint4(0u, 0u, 0u, 0u);
     }
 }
 
@@ -176,6 +185,7 @@ constexpr int SLOT_ITEMS = FLUID_SLOT_ITEMS;
 __global__ void __launch_bounds__(GATHER_THREADS)
 k_cell_slots(uint32_t n, uint32_t num_cells, const uint32_t* __restrict__ keys_u, uint32_t* __restrict__ cursor,
              uint32_t* __restrict__ slot_keys, uint32_t* __restrict__ slot_idx) {
+    pdl_enter();
     const uint32_t lane = lane_id();
     const uint32_t warp = (blockIdx.x * GATHER_THREADS + threadIdx.x) >> 5;
     const uint32_t first = warp * (32u * SLOT_ITEMS) + lane;
@@ -231,7 +241,16 @@ k_rank_gather_cells(const DevParams p, const uint32_t* __restrict__ slot_keys, c
                     float2* __restrict__ pos_s, float2* __restrict__ pred_s, float2* __restrict__ vel_s,
                     uint32_t* __restrict__ start_indices,
                     const uint32_t* __restrict__ cell_lb, uint32_t* __restrict__ quirk,
-                    const uint32_t* __restrict__ frame_time) {
+                    const uint32_t* __restrict__ frame_time, TilePlan* __restrict__ plans) {
+    pdl_enter();
+    // the staging plans of the neighbour passes for the tiles this CTA's slots cover (k_tile_plans as a separate launch
+    // costs one more kernel boundary per tick): they depend on the slot keys and cell_lb only, both final by now
+    {
+        constexpr uint32_t TILES_PER_CTA = GATHER_THREADS * RANK_ITEMS / SPH_THREADS;
+        static_assert(GATHER_THREADS * RANK_ITEMS % SPH_THREADS == 0, "a CTA covers whole tiles");
+        const uint32_t tile = blockIdx.x * TILES_PER_CTA + threadIdx.x;
+        if (threadIdx.x < TILES_PER_CTA && tile * SPH_THREADS < p.n) make_tile_plan(p, slot_keys, cell_lb, tile, plans);
+    }
     const uint32_t q0 = blockIdx.x * (GATHER_THREADS * RANK_ITEMS) + threadIdx.x;
     uint32_t kc[RANK_ITEMS], src[RANK_ITEMS], lo[RANK_ITEMS], hi[RANK_ITEMS], rank[RANK_ITEMS];
     float2 ps[RANK_ITEMS], vs[RANK_ITEMS];

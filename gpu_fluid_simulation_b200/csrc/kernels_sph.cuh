@@ -59,12 +59,9 @@ struct __align__(16) TilePlan {
 };
 static_assert(sizeof(TilePlan) == 64, "TilePlan is read as four 16-byte words");
 
-__global__ void __launch_bounds__(128)
-k_tile_plans(const DevParams p, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ lb, uint32_t ntiles,
-             TilePlan* __restrict__ plans) {
+__device__ __forceinline__ void make_tile_plan(const DevParams& p, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ lb,
+                                               uint32_t tile, TilePlan* __restrict__ plans) {
     constexpr int NI = SPH_MAX_ROWS * 3;
-    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tile >= ntiles) return;
     const uint32_t i0 = p.own_begin + tile * SPH_THREADS;
     const uint32_t i1 = min(i0 + SPH_THREADS, p.own_begin + p.n);
     const uint32_t kf = min(__ldg(keys + i0), p.num_cells - 1u), kl = min(__ldg(keys + i1 - 1u), p.num_cells - 1u);
@@ -116,6 +113,14 @@ k_tile_plans(const DevParams p, const uint32_t* __restrict__ keys, const uint32_
     uint4* dst = reinterpret_cast<uint4*>(plans + tile);
 #pragma unroll
     for (int q = 0; q < 4; q++) dst[q] = src[q];
+}
+
+__global__ void __launch_bounds__(128)
+k_tile_plans(const DevParams p, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ lb, uint32_t ntiles,
+             TilePlan* __restrict__ plans) {
+    pdl_enter();
+    const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tile < ntiles) make_tile_plan(p, keys, lb, tile, plans);
 }
 
 // thread 0 of a CTA: read the tile's plan, publish the staging bases, issue the copies.
@@ -290,6 +295,7 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
     __shared__ __align__(128) float2 s_pred[SPH_CAP + 2];  // + pad: the pair loop may load one record past a span
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
+    pdl_enter();
     // slab mode: owned particles are [own_begin, own_begin + n) of arrays that also hold halo rows on both sides
     const uint32_t i0 = p.own_begin + blockIdx.x * SPH_THREADS;
     const uint32_t i1 = min(i0 + SPH_THREADS, p.own_begin + p.n);
@@ -813,6 +819,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     __shared__ uint16_t s_list[FORCE_LIST * SPH_THREADS];
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
+    pdl_enter();
     // slab mode: owned particles are [own_begin, own_begin + n) of arrays that also hold halo rows on both sides
     const uint32_t i0 = p.own_begin + blockIdx.x * SPH_THREADS;
     const uint32_t i1 = min(i0 + SPH_THREADS, p.own_begin + p.n);

@@ -42,7 +42,10 @@ struct Sim {
     uint32_t* quirk = nullptr;          // [0] lowest occupied cell c0, [1] its stale start_indices entry
 
     // counting sort over the cells (kernels_count.cuh): per-cell counts / write cursors, zero-padded to whole scan tiles
-    uint32_t* cell_count = nullptr;
+    uint32_t* cell_count = nullptr;              // the array the current tick counts into (one of the two below)
+    uint32_t* cell_count_buf[2] = {nullptr, nullptr};  // alternate per counted tick; the scan clears the other one
+    int cell_count_cur = 0;
+    bool pdl = true;                             // programmatic dependent launch on the tick's kernels (FLUID_NO_PDL=1: off)
     uint32_t *cell_tile_sum = nullptr, *cell_tile_max = nullptr;
     uint32_t cell_tiles = 0;
     volatile uint32_t* cell_max_host = nullptr;  // pinned + mapped: largest cell population of the latest completed scan
