@@ -265,9 +265,9 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
         launch_pdl(pdl, k_predict_key_count, dim3(blocks), dim3(HASH_THREADS), stream, p, pos_a, vel_a, keys_u, cell_count, d_frame_time);
         launches++;
         mark("predict+key+hist");
-        launch_pdl(pdl, k_cell_reduce, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_tile_sum, cell_tile_max);
+        launch_pdl(pdl, k_cell_reduce, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_tile_sum, cell_tile_max, cell_tile_sq);
         launch_pdl(pdl, k_cell_downsweep, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_lb, cell_tile_sum,
-                   cell_tile_max, cell_tiles, cell_max_dev, count_next);
+                   cell_tile_max, cell_tile_sq, cell_tiles, cell_max_dev, count_next);
         launches += 2;
         if (sort_mode == FLUID_SORT_COUNTING) {
             counting = true;
@@ -277,7 +277,11 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
                 FLUID_CUDA(cudaStreamSynchronize(stream));
                 cell_max_known = true;
             }
-            counting = *cell_max_host <= COUNT_SORT_MAX_CELL;
+            const uint32_t max_ok = std::min(std::max(n / 1024u, COUNT_SORT_MAX_CELL_LO), COUNT_SORT_MAX_CELL_HI);
+            const uint32_t sq_bits = cell_max_host[1];
+            float sum_sq;
+            memcpy(&sum_sq, &sq_bits, 4);
+            counting = cell_max_host[0] <= max_ok && sum_sq <= COUNT_SORT_MAX_MEAN_SQ * (float)n;
         }
     }
     if (counting) {
@@ -422,7 +426,8 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
         cudaMalloc(&sim->cell_count_buf[1], cells_padded * 4) != cudaSuccess ||
         cudaMalloc(&sim->cell_tile_sum, (size_t)sim->cell_tiles * 4) != cudaSuccess ||
         cudaMalloc(&sim->cell_tile_max, (size_t)sim->cell_tiles * 4) != cudaSuccess ||
-        cudaHostAlloc((void**)&sim->cell_max_host, 4, cudaHostAllocMapped) != cudaSuccess ||
+        cudaMalloc(&sim->cell_tile_sq, (size_t)sim->cell_tiles * 4) != cudaSuccess ||
+        cudaHostAlloc((void**)&sim->cell_max_host, 8, cudaHostAllocMapped) != cudaSuccess ||
         cudaHostGetDevicePointer((void**)&sim->cell_max_dev, (void*)sim->cell_max_host, 0) != cudaSuccess ||
         cudaMalloc(&sim->quirk, 16) != cudaSuccess || cudaMalloc(&sim->d_frame_time, 4) != cudaSuccess ||
         cudaMalloc(&sim->force_field, tex_len * 8) != cudaSuccess)
@@ -432,7 +437,8 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
     cudaMemsetAsync(sim->cell_lb, 0, cells_padded * 4, sim->stream);
     cudaMemsetAsync(sim->cell_count_buf[0], 0, cells_padded * 4, sim->stream);
     cudaMemsetAsync(sim->cell_count_buf[1], 0, cells_padded * 4, sim->stream);
-    *sim->cell_max_host = 0;
+    sim->cell_max_host[0] = 0;
+    sim->cell_max_host[1] = 0;
     {
         const char* no_pdl = getenv("FLUID_NO_PDL");
         sim->pdl = !(no_pdl && no_pdl[0] == '1');
@@ -478,7 +484,7 @@ void fluid_sim_destroy(FluidSim* h) {
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
                     s->idx_b, s->sort_scratch, s->tile_plans, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
                     s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta,
-                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max};
+                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq};
     for (void* b : bufs) if (b) cudaFree(b);
     if (s->cell_max_host) cudaFreeHost((void*)s->cell_max_host);
     for (auto& row : s->mark_events) for (auto& e : row) if (e) cudaEventDestroy(e);

@@ -25,7 +25,19 @@
 
 namespace fluid {
 
-constexpr int SPH_THREADS = 256;
+#ifndef FLUID_SPH_THREADS
+#define FLUID_SPH_THREADS 256
+#endif
+#if FLUID_SPH_THREADS == 256
+#define FLUID_LIST_STRIDE 512
+#define FLUID_LIST_STRIDE_STR "512"
+#elif FLUID_SPH_THREADS == 128
+#define FLUID_LIST_STRIDE 256
+#define FLUID_LIST_STRIDE_STR "256"
+#else
+#error "FLUID_SPH_THREADS must be 128 or 256"
+#endif
+constexpr int SPH_THREADS = FLUID_SPH_THREADS;  // sorted particles per CTA of the neighbour passes (= tile of the staging plans)
 #ifndef FLUID_SPH_CAP
 #define FLUID_SPH_CAP 1536
 #endif
@@ -685,7 +697,7 @@ __device__ __forceinline__ void scan_span(uint32_t& addr, uint32_t end, uint32_t
         "setp.leu.f32 hit, s, %6;\n"
         "cvt.u16.u32 lo, %0;\n"
         "@hit st.shared.u16 [%1], lo;\n"
-        "@hit add.u32 %1, %1, 512;\n"
+        "@hit add.u32 %1, %1, " FLUID_LIST_STRIDE_STR ";\n"
         "add.u32 %0, %0, 8;\n"
         "setp.lt.u32 go, %0, %2;\n"
         "setp.lt.and.u32 go, %1, %3, go;\n"
@@ -708,7 +720,7 @@ __device__ __forceinline__ void scan_span2(uint32_t& addr, uint32_t end, uint32_
         ".reg .b16 la, lb;\n"
         ".reg .u32 nx, e2, w2;\n"
         "add.u32 e2, %2, -8;\n"
-        "add.u32 w2, %3, -512;\n"
+        "add.u32 w2, %3, -" FLUID_LIST_STRIDE_STR ";\n"
         "setp.lt.s32 go, %0, e2;\n"          // shared-window addresses are < 2^31: signed compare survives end - 8 < 0
         "setp.lt.and.s32 go, %1, w2, go;\n"
         "@!go bra SCAN2_DONE;\n"
@@ -731,9 +743,9 @@ __device__ __forceinline__ void scan_span2(uint32_t& addr, uint32_t end, uint32_
         "cvt.u16.u32 la, %0;\n"
         "cvt.u16.u32 lb, nx;\n"
         "@ha st.shared.u16 [%1], la;\n"
-        "@ha add.u32 %1, %1, 512;\n"
+        "@ha add.u32 %1, %1, " FLUID_LIST_STRIDE_STR ";\n"
         "@hb st.shared.u16 [%1], lb;\n"
-        "@hb add.u32 %1, %1, 512;\n"
+        "@hb add.u32 %1, %1, " FLUID_LIST_STRIDE_STR ";\n"
         "add.u32 %0, %0, 16;\n"
         "setp.lt.s32 go, %0, e2;\n"
         "setp.lt.and.s32 go, %1, w2, go;\n"
@@ -744,7 +756,7 @@ __device__ __forceinline__ void scan_span2(uint32_t& addr, uint32_t end, uint32_
         : "r"(end), "r"(wr_end), "f"(px), "f"(py), "f"(h2)
         : "memory");
 }
-static_assert(SPH_THREADS * 2 == 512, "scan_span hard-codes the list column stride");
+static_assert(SPH_THREADS * 2 == FLUID_LIST_STRIDE, "scan_span takes the list column stride as a literal");
 
 template <bool DEBUG, bool EXACT>
 __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t sp_addr, uint32_t sv_addr, uint32_t sr_addr,

@@ -47,8 +47,9 @@ struct Sim {
     int cell_count_cur = 0;
     bool pdl = true;                             // programmatic dependent launch on the tick's kernels (FLUID_NO_PDL=1: off)
     uint32_t *cell_tile_sum = nullptr, *cell_tile_max = nullptr;
+    float* cell_tile_sq = nullptr;
     uint32_t cell_tiles = 0;
-    volatile uint32_t* cell_max_host = nullptr;  // pinned + mapped: largest cell population of the latest completed scan
+    volatile uint32_t* cell_max_host = nullptr;  // pinned + mapped, 2 words: largest cell population and sum of squared populations (float bits) of the latest completed scan
     uint32_t* cell_max_dev = nullptr;            // device alias of cell_max_host
     bool cell_max_known = false;                 // false after anything that replaces the state (upload, resize)
     int sort_mode = FLUID_SORT_AUTO;

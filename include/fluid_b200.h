@@ -150,8 +150,9 @@ int fluid_sim_get_math_mode(const FluidSim* sim);
  *   exclusive scan that IS the cell table, slot assignment, then each cell's few entries ranked by source index.
  *   Cost grows with the square of a cell's population.
  * FLUID_SORT_RADIX: onesweep LSD radix passes over (key, index); cost independent of the distribution.
- * FLUID_SORT_AUTO (default): counting while the most crowded cell holds <= 64 particles (watched per tick without a
- *   sync; one stream sync on the first tick after an upload), radix otherwise. Slab mode always uses the radix passes.
+ * FLUID_SORT_AUTO (default): counting while the most crowded cell holds <= clamp(n / 1024, 64, 4096) particles and the
+ *   squared cell populations sum to <= 128 n (both watched per tick without a sync; one stream sync on the first tick
+ *   after an upload), radix otherwise. Slab mode always uses the radix passes.
  * fluid_sim_last_sort_path: which of the two the most recently enqueued tick used. */
 #define FLUID_SORT_AUTO 0
 #define FLUID_SORT_RADIX 1
