@@ -170,7 +170,7 @@ def main():
                     help="key-order path of the single-GPU tick (include/fluid_b200.h FLUID_SORT_*): identical results")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--e2e-steps", type=int, default=6)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -283,23 +283,40 @@ def main():
     e2e = None
     if not args.no_e2e:
         host_in = torch.empty((n, 8), dtype=torch.float32).pin_memory()
-        host_out = torch.empty((n, 8), dtype=torch.float32).pin_memory()
+        host_outs = [torch.empty((n, 8), dtype=torch.float32).pin_memory() for _ in range(2)]
+        out_views = [h.numpy().view(fluid.PARTICLE_DTYPE).reshape(-1) for h in host_outs]
         init = sim.download_particles()
         host_in.numpy().view(np.uint8).reshape(-1)[:] = init.view(np.uint8).reshape(-1)
         del init
-        k = max(1, args.e2e_steps)
-        for _ in range(1):
-            sim.upload_particles(host_in); sim.tick(ts); sim.download_particles(out=host_out.numpy().view(fluid.PARTICLE_DTYPE).reshape(-1))
+        k = max(2, args.e2e_steps)
+        # (a) the calls one after the other: upload, tick, download (which synchronises)
+        sim.upload_particles(host_in); sim.tick(ts); sim.download_particles(out=out_views[0])
+        ks = 2
         t0 = time.perf_counter()
-        for _ in range(k):
+        for j in range(ks):
             sim.upload_particles(host_in)
             sim.tick(ts)
-            sim.download_particles(out=host_out.numpy().view(fluid.PARTICLE_DTYPE).reshape(-1))  # synchronises
+            sim.download_particles(out=out_views[j & 1])  # synchronises
+        dt_serial = time.perf_counter() - t0
+        # (b) the same three calls per step through the pipelined variants: every step still uploads its full input
+        # state from pinned host memory and downloads its full result, but the upload of step k+1 runs on its own copy
+        # stream while the result of step k goes back (PCIe is full duplex); results alternate between two host buffers
+        sim.upload_particles_async(host_in); sim.tick(ts); sim.download_particles_async(out_views[0]); sim.sync_transfers()
+        t0 = time.perf_counter()
+        for j in range(k):
+            sim.upload_particles_async(host_in)
+            sim.tick(ts)
+            sim.download_particles_async(out_views[j & 1])
+        sim.sync_transfers()
         dt = time.perf_counter() - t0
         e2e = {"value": n * k / dt, "unit": "particle-steps/s", "h2d_bytes_per_step": n * 32 + 60, "d2h_bytes_per_step": n * 32,
                "steps": k, "ms_per_step": 1e3 * dt / k,
-               "note": "upload_particles (pinned host AoS) + tick + download_particles (pinned host AoS) every step"}
-        del host_in, host_out
+               "note": "upload_particles_async (pinned host AoS) + tick + download_particles_async (pinned host AoS) every step, "
+                       "one fluid_sim_sync_transfers after the last step; the upload of the next input overlaps the download of the previous result",
+               "serial": {"value": n * ks / dt_serial, "ms_per_step": 1e3 * dt_serial / ks, "steps": ks,
+                          "note": "upload_particles + tick + download_particles, each call complete before the next"}}
+        host_out = None
+        del host_in, host_outs, out_views, host_out
         # the reference's own per-frame call pattern, for comparison (extra key, NOT the contract's e2e): the particle
         # state stays on the device as it does in the reference; per frame the host uploads the force field
         # (queue.write_buffer, src/renderer.rs:498-502), calls tick with host TickSettings, and receives the frame

@@ -92,6 +92,9 @@ PROTOTYPES = {
     "fluid_sim_grid_h": (_u32, [_P]),
     "fluid_sim_download_particles": (_i, [_P, _P]),
     "fluid_sim_upload_particles": (_i, [_P, _P]),
+    "fluid_sim_upload_particles_async": (_i, [_P, _P]),
+    "fluid_sim_download_particles_async": (_i, [_P, _P]),
+    "fluid_sim_sync_transfers": (_i, [_P]),
     "fluid_sim_download_start_indices": (_i, [_P, _P]),
     "fluid_sim_upload_start_indices": (_i, [_P, _P]),
     "fluid_sim_upload_force_field": (_i, [_P, _P]),

@@ -487,6 +487,11 @@ void fluid_sim_destroy(FluidSim* h) {
                     s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq};
     for (void* b : bufs) if (b) cudaFree(b);
     if (s->cell_max_host) cudaFreeHost((void*)s->cell_max_host);
+    if (s->h2d_stream) { cudaStreamSynchronize(s->h2d_stream); cudaStreamDestroy(s->h2d_stream); }
+    if (s->d2h_stream) { cudaStreamSynchronize(s->d2h_stream); cudaStreamDestroy(s->d2h_stream); }
+    if (s->aos_in) cudaFree(s->aos_in);
+    if (s->aos_out) cudaFree(s->aos_out);
+    for (cudaEvent_t e : {s->ev_h2d_done, s->ev_in_free, s->ev_out_ready, s->ev_d2h_done}) if (e) cudaEventDestroy(e);
     for (auto& row : s->mark_events) for (auto& e : row) if (e) cudaEventDestroy(e);
     if (s->stream) cudaStreamDestroy(s->stream);
     cudaGetLastError();
@@ -572,6 +577,64 @@ int fluid_sim_upload_particles(FluidSim* h, const FluidParticle* src) {
     FLUID_CUDA(cudaGetLastError());
     // the source buffer may be pageable: the copy above is then already complete on return; for pinned
     // memory the caller must not modify `src` before the next fluid_sim_sync / download.
+    return FLUID_OK;
+}
+static int ensure_pipeline(Sim* s) {
+    if (!s->h2d_stream) {
+        FLUID_CUDA(cudaStreamCreateWithFlags(&s->h2d_stream, cudaStreamNonBlocking));
+        FLUID_CUDA(cudaStreamCreateWithFlags(&s->d2h_stream, cudaStreamNonBlocking));
+        cudaEvent_t* evs[] = {&s->ev_h2d_done, &s->ev_in_free, &s->ev_out_ready, &s->ev_d2h_done};
+        for (cudaEvent_t* e : evs) FLUID_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+    }
+    if (!s->aos_in) {  // first use, or dropped by fluid_sim_reserve
+        FLUID_CUDA(cudaMalloc(&s->aos_in, ((size_t)s->capacity + 64) * sizeof(FluidParticle)));
+        FLUID_CUDA(cudaMalloc(&s->aos_out, ((size_t)s->capacity + 64) * sizeof(FluidParticle)));
+        s->in_used = s->out_used = false;
+    }
+    return FLUID_OK;
+}
+int fluid_sim_upload_particles_async(FluidSim* h, const FluidParticle* src) {
+    SIM_OR_FAIL(h);
+    NOT_SLAB(s);
+    if (!src) return invalid("fluid_sim_upload_particles_async: null source");
+    int rc = ensure_pipeline(s);
+    if (rc != FLUID_OK) return rc;
+    // the copy stream may overwrite the staging buffer once the previous transposition out of it has run
+    if (s->in_used) FLUID_CUDA(cudaStreamWaitEvent(s->h2d_stream, s->ev_in_free, 0));
+    FLUID_CUDA(cudaMemcpyAsync(s->aos_in, src, (size_t)s->n * sizeof(FluidParticle), cudaMemcpyHostToDevice, s->h2d_stream));
+    FLUID_CUDA(cudaEventRecord(s->ev_h2d_done, s->h2d_stream));
+    FLUID_CUDA(cudaStreamWaitEvent(s->stream, s->ev_h2d_done, 0));
+    k_aos_to_soa<<<(s->n + 255) / 256, 256, 0, s->stream>>>(s->aos_in, s->n, s->pos_a, s->pred_s, s->vel_a, s->rho, s->keys_view());
+    s->launches++;
+    FLUID_CUDA(cudaEventRecord(s->ev_in_free, s->stream));
+    s->in_used = true;
+    s->cell_max_known = false;
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+int fluid_sim_download_particles_async(FluidSim* h, FluidParticle* dst) {
+    SIM_OR_FAIL(h);
+    NOT_SLAB(s);
+    if (!dst) return invalid("fluid_sim_download_particles_async: null destination");
+    int rc = ensure_pipeline(s);
+    if (rc != FLUID_OK) return rc;
+    // the transposition may overwrite the staging buffer once the previous device-to-host copy out of it is done
+    if (s->out_used) FLUID_CUDA(cudaStreamWaitEvent(s->stream, s->ev_d2h_done, 0));
+    k_soa_to_aos<<<(s->n + 255) / 256, 256, 0, s->stream>>>(s->aos_out, s->n, s->pos_a, s->pred_s, s->vel_a, s->rho, s->keys_view());
+    s->launches++;
+    FLUID_CUDA(cudaEventRecord(s->ev_out_ready, s->stream));
+    FLUID_CUDA(cudaStreamWaitEvent(s->d2h_stream, s->ev_out_ready, 0));
+    FLUID_CUDA(cudaMemcpyAsync(dst, s->aos_out, (size_t)s->n * sizeof(FluidParticle), cudaMemcpyDeviceToHost, s->d2h_stream));
+    FLUID_CUDA(cudaEventRecord(s->ev_d2h_done, s->d2h_stream));
+    s->out_used = true;
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+int fluid_sim_sync_transfers(FluidSim* h) {
+    SIM_OR_FAIL(h);
+    if (s->h2d_stream) FLUID_CUDA(cudaStreamSynchronize(s->h2d_stream));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    if (s->d2h_stream) FLUID_CUDA(cudaStreamSynchronize(s->d2h_stream));
     return FLUID_OK;
 }
 int fluid_sim_download_start_indices(FluidSim* h, uint32_t* dst) {
@@ -715,6 +778,13 @@ int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
     SIM_OR_FAIL(h);
     NOT_SLAB(s);
     if (capacity <= s->capacity) return FLUID_OK;
+    if (s->aos_in) {  // pipelined-transfer staging is sized by the capacity: drain and drop, re-created on next use
+        FLUID_CUDA(cudaStreamSynchronize(s->h2d_stream));
+        FLUID_CUDA(cudaStreamSynchronize(s->stream));
+        FLUID_CUDA(cudaStreamSynchronize(s->d2h_stream));
+        cudaFree(s->aos_in); cudaFree(s->aos_out);
+        s->aos_in = s->aos_out = nullptr;
+    }
     // contents are preserved through a host-free device round trip of the live arrays
     const uint32_t n = s->n;
     float2 *pa = nullptr, *va = nullptr, *pr = nullptr; float* rh = nullptr; uint32_t* ks = nullptr;

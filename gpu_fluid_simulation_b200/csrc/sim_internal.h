@@ -58,6 +58,12 @@ struct Sim {
     float2* force_field = nullptr;      // reference `texture` (src/simulation.rs:213-218)
 
     FluidParticle* aos_stage = nullptr;
+    // pipelined transfers (fluid_sim_upload_particles_async / _download_particles_async): own copy streams and staging
+    // buffers, so that the upload of the next state overlaps the download of the previous result (PCIe is full duplex)
+    cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+    FluidParticle *aos_in = nullptr, *aos_out = nullptr;
+    cudaEvent_t ev_h2d_done = nullptr, ev_in_free = nullptr, ev_out_ready = nullptr, ev_d2h_done = nullptr;
+    bool in_used = false, out_used = false;
     float2 *dbg_accel = nullptr, *dbg_abs = nullptr;
     bool debug_force = false;
     bool exact_math = true;   // FLUID_MATH_EXACT / FLUID_MATH_FAST

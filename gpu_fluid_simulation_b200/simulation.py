@@ -197,6 +197,20 @@ class FluidSimulation:
             particles = np.ascontiguousarray(particles)
         _lib.check(self._lib.fluid_sim_upload_particles(self._h, _lib.ptr(particles)))
 
+    # pipelined transfers: copies on the handle's own streams, upload of the next state overlapping the download of
+    # the previous result; buffers should be pinned and stay untouched until sync_transfers()
+    def upload_particles_async(self, particles):
+        if isinstance(particles, np.ndarray):
+            assert particles.dtype == PARTICLE_DTYPE and particles.shape == (self.particle_count,)
+            assert particles.flags["C_CONTIGUOUS"]
+        _lib.check(self._lib.fluid_sim_upload_particles_async(self._h, _lib.ptr(particles)))
+
+    def download_particles_async(self, out):
+        _lib.check(self._lib.fluid_sim_download_particles_async(self._h, _lib.ptr(out)))
+
+    def sync_transfers(self):
+        _lib.check(self._lib.fluid_sim_sync_transfers(self._h))
+
     def download_start_indices(self) -> np.ndarray:
         out = np.empty(self.grid_w * self.grid_h, dtype=np.uint32)
         _lib.check(self._lib.fluid_sim_download_start_indices(self._h, _lib.ptr(out)))

@@ -175,6 +175,16 @@ uint32_t fluid_sim_grid_h(const FluidSim* sim);
 /* binding 0 of simulation_bg: N x 32 B AoS, in the current (sorted) physical order. */
 int fluid_sim_download_particles(FluidSim* sim, FluidParticle* dst);
 int fluid_sim_upload_particles(FluidSim* sim, const FluidParticle* src);
+/* Pipelined variants for callers that stream whole states through the device (the reference never does: its state
+ * lives in wgpu buffers, src/simulation.rs:168-172; this is the boundary's host-buffer path made full duplex).
+ * Copies run on the handle's own copy streams through separate staging buffers, ordered against the tick stream by
+ * events: the upload of the next state overlaps the download of the previous result. `src` / `dst` should be pinned
+ * (pageable memory degrades to synchronous copies) and must stay untouched until fluid_sim_sync_transfers returns or,
+ * for `src`, until the next _upload_particles_async on the same handle has been issued AND a later sync returned.
+ * Not available in slab mode. */
+int fluid_sim_upload_particles_async(FluidSim* sim, const FluidParticle* src);
+int fluid_sim_download_particles_async(FluidSim* sim, FluidParticle* dst);
+int fluid_sim_sync_transfers(FluidSim* sim);
 /* binding 1: grid_w*grid_h u32, reference semantics (never cleared, compute.wgsl:45-56). */
 int fluid_sim_download_start_indices(FluidSim* sim, uint32_t* dst);
 int fluid_sim_upload_start_indices(FluidSim* sim, const uint32_t* src);
