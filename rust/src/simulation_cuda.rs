@@ -48,6 +48,11 @@ extern "C" {
     fn fluid_sim_field_from_mask(sim: *mut FluidSim, mask: *const u8, seeds_out: *mut u32, field_xy_out: *mut f32, ms_out: *mut f32) -> c_int;
     fn fluid_sim_render(sim: *mut FluidSim, inv_proj: *const f32, w: u32, h: u32, rgba_f32_out: *mut f32, rgba8_out: *mut u8, ms_out: *mut f32) -> c_int;
     fn fluid_sim_surface_tension(sim: *mut FluidSim, force_xy_out: *mut f32) -> c_int;
+    fn fluid_sim_set_sort_mode(sim: *mut FluidSim, mode: c_int) -> c_int;
+    fn fluid_sim_last_sort_path(sim: *const FluidSim) -> c_int;
+    fn fluid_sim_upload_particles_async(sim: *mut FluidSim, src: *const ParticleInstance) -> c_int;
+    fn fluid_sim_download_particles_async(sim: *mut FluidSim, dst: *mut ParticleInstance) -> c_int;
+    fn fluid_sim_sync_transfers(sim: *mut FluidSim) -> c_int;
 }
 
 fn check(rc: c_int) {
@@ -120,6 +125,20 @@ impl FluidSimulation {
         v
     }
     /// reference: Renderer::restart_simulation, src/renderer.rs:870-872
+    /// 0 = auto (counting sort over the cells unless they are crowded), 1 = radix passes, 2 = counting; same order either way.
+    pub fn set_sort_mode(&mut self, mode: i32) { check(unsafe { fluid_sim_set_sort_mode(self.handle, mode) }); }
+    pub fn last_sort_path(&self) -> i32 { unsafe { fluid_sim_last_sort_path(self.handle) } }
+    /// Pipelined whole-state transfers (pinned slices; untouched until `sync_transfers`): the upload of the next state
+    /// overlaps the download of the previous result.
+    pub unsafe fn upload_particles_async(&mut self, src: &[ParticleInstance]) {
+        assert_eq!(src.len(), self.settings.particle_count as usize);
+        check(fluid_sim_upload_particles_async(self.handle, src.as_ptr()));
+    }
+    pub unsafe fn download_particles_async(&mut self, dst: &mut [ParticleInstance]) {
+        assert_eq!(dst.len(), self.settings.particle_count as usize);
+        check(fluid_sim_download_particles_async(self.handle, dst.as_mut_ptr()));
+    }
+    pub fn sync_transfers(&mut self) { check(unsafe { fluid_sim_sync_transfers(self.handle) }); }
     pub fn restart(&mut self, device_ordinal: i32) { *self = Self::new(device_ordinal, self.settings); }
     pub fn cuda_stream(&mut self) -> *mut c_void { unsafe { fluid_sim_stream(self.handle) } }
 }
