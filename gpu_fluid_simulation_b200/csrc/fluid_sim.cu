@@ -286,7 +286,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     }
     if (counting) {
         launch_pdl(pdl, k_cell_slots, dim3((n + GATHER_THREADS * SLOT_ITEMS - 1) / (GATHER_THREADS * SLOT_ITEMS)), dim3(GATHER_THREADS),
-                   stream, n, p.num_cells, keys_u, cell_count, keys_b, idx_a);
+                   stream, n, 0u, p.num_cells - 1u, keys_u, cell_count, keys_b, idx_a);
         launches++;
         mark("sort");
         launch_pdl(pdl, k_rank_gather_cells, dim3((n + GATHER_THREADS * RANK_ITEMS - 1) / (GATHER_THREADS * RANK_ITEMS)),
@@ -484,7 +484,7 @@ void fluid_sim_destroy(FluidSim* h) {
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
                     s->idx_b, s->sort_scratch, s->tile_plans, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
                     s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta,
-                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq};
+                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq, s->slab_bin_lb};
     for (void* b : bufs) if (b) cudaFree(b);
     if (s->cell_max_host) cudaFreeHost((void*)s->cell_max_host);
     if (s->h2d_stream) { cudaStreamSynchronize(s->h2d_stream); cudaStreamDestroy(s->h2d_stream); }
@@ -816,6 +816,7 @@ int fluid_sim_set_particle_count(FluidSim* h, uint32_t n) {
     if (s->slab) {
         if (n > s->slab_capacity) return invalid("fluid_sim_set_particle_count: n exceeds the slab capacity");
         s->n = n;
+        s->cell_max_known = false;
         return FLUID_OK;
     }
     if (n < 2 || n > s->capacity) return invalid("fluid_sim_set_particle_count: need 2 <= n <= capacity");

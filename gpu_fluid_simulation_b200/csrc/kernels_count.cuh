@@ -37,6 +37,10 @@ constexpr uint32_t CELL_SCAN_TILE = CELL_SCAN_THREADS * CELL_SCAN_ITEMS;
 constexpr uint32_t COUNT_SORT_MAX_CELL_LO = 64, COUNT_SORT_MAX_CELL_HI = 4096;
 constexpr float COUNT_SORT_MAX_MEAN_SQ = 128.0f;
 
+__device__ __forceinline__ uint32_t count_bin(uint32_t key, uint32_t key_lo, uint32_t last_bin) {
+    return min(key - min(key, key_lo), last_bin);
+}
+
 // count[cell] += 1 for every valid lane; the first lane of every run of equal cells adds the run's length
 __device__ __forceinline__ void cell_count_add(uint32_t* __restrict__ count, uint32_t cell, bool valid) {
     const uint32_t lane = lane_id();
@@ -213,8 +217,10 @@ k_cell_downsweep(uint32_t* __restrict__ count_cursor, uint32_t* __restrict__ cel
 #endif
 constexpr int SLOT_ITEMS = FLUID_SLOT_ITEMS;
 __global__ void __launch_bounds__(GATHER_THREADS)
-k_cell_slots(uint32_t n, uint32_t num_cells, const uint32_t* __restrict__ keys_u, uint32_t* __restrict__ cursor,
+k_cell_slots(uint32_t n, uint32_t key_lo, uint32_t last_bin, const uint32_t* __restrict__ keys_u, uint32_t* __restrict__ cursor,
              uint32_t* __restrict__ slot_keys, uint32_t* __restrict__ slot_idx) {
+    // bin of a key = clamp(key - key_lo, 0, last_bin): (0, num_cells - 1) on one GPU; a slab rank passes its band's first
+    // cell and one bin past its last for the sentinel key of emigrants (count_bin)
     pdl_enter();
     const uint32_t lane = lane_id();
     const uint32_t warp = (blockIdx.x * GATHER_THREADS + threadIdx.x) >> 5;
@@ -229,7 +235,7 @@ k_cell_slots(uint32_t n, uint32_t num_cells, const uint32_t* __restrict__ keys_u
 #pragma unroll
     for (int j = 0; j < SLOT_ITEMS; j++) {
         const bool valid = first + j * 32u < n;
-        const uint32_t kc = min(k[j], num_cells - 1u);
+        const uint32_t kc = count_bin(k[j], key_lo, last_bin);
         const uint32_t d = valid ? kc : 0xffffffffu;
         const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
         const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0u || d != prev);
@@ -328,6 +334,17 @@ k_rank_gather_cells(const DevParams p, const uint32_t* __restrict__ slot_keys, c
             }
         }
     }
+}
+
+// slab mode: the keys exist already (k_slab_key_hist makes them while it detects emigrants); count them per bin.
+// The last bin belongs to the sentinel key of emigrants: they are NOT counted, so the scan's statistics cover real cells
+// only and the last bin starts at the owned count; the slot pass still hands them (unused) slots behind it.
+__global__ void __launch_bounds__(GATHER_THREADS)
+k_count_keys(const uint32_t* __restrict__ keys, uint32_t n, uint32_t key_lo, uint32_t last_bin, uint32_t* __restrict__ count) {
+    const uint32_t i = blockIdx.x * GATHER_THREADS + threadIdx.x;  // grid is a whole number of warps
+    const uint32_t k = i < n ? __ldg(keys + i) : 0u;
+    const uint32_t bin = count_bin(k, key_lo, last_bin);
+    cell_count_add(count, bin, i < n && bin != last_bin);
 }
 
 // the source permutation (sorted index -> index before the tick) is a parity tap only: computed on request from the

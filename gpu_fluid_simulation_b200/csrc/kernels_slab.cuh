@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "kernels_cells.cuh"
 #include "kernels_hash.cuh"
+#include "kernels_count.cuh"
 #include "slab_rows.h"
 
 namespace fluid {
@@ -87,6 +88,35 @@ k_slab_gather(const DevParams p, const uint32_t* __restrict__ sorted_keys, const
     pred_s[o] = pr;
     keys_ext[o] = __ldg(sorted_keys + i);
     // wild stamp of this tick (common.cuh tame_component); halo rows are tested where their keys are made
+    if (!(tame_component(pr.x) && tame_component(pr.y) && tame_component(vs.x) && tame_component(vs.y))) *wild_stamp = __ldg(frame_time);
+}
+// counting path (kernels_count.cuh): per slot of [from below | natives | from above] in arrival order: rank inside its
+// bin by source index = the stable order of the radix passes; emigrants carry the sentinel key, sit in the last bin
+// (positions >= p.n) and are dropped. Same outputs as k_slab_gather.
+__global__ void __launch_bounds__(GATHER_THREADS)
+k_slab_rank_gather(const DevParams p, uint32_t total, uint32_t key_lo, uint32_t last_bin, const uint32_t* __restrict__ slot_keys,
+                   const uint32_t* __restrict__ slot_idx, const uint32_t* __restrict__ bin_lb,
+                   const float2* __restrict__ pos_in, const float2* __restrict__ vel_in, float2* __restrict__ pos_s,
+                   float2* __restrict__ pred_s, float2* __restrict__ vel_s, uint32_t* __restrict__ keys_ext,
+                   uint32_t* __restrict__ wild_stamp, const uint32_t* __restrict__ frame_time) {
+    const uint32_t q = blockIdx.x * GATHER_THREADS + threadIdx.x;
+    if (q >= total) return;
+    const uint32_t k = __ldg(slot_keys + q);
+    const uint32_t bin = count_bin(k, key_lo, last_bin);
+    if (bin == last_bin) return;  // emigrant
+    const uint32_t lo = __ldg(bin_lb + bin), hi = __ldg(bin_lb + bin + 1u);
+    const uint32_t src = __ldg(slot_idx + q);
+    const float2 ps = __ldg(pos_in + src), vs = __ldg(vel_in + src);
+    uint32_t rank = 0;
+    for (uint32_t j = lo; j < hi; j++) rank += (__ldg(slot_idx + j) < src) ? 1u : 0u;
+    const uint32_t i = lo + rank;
+    if (i >= p.n) return;
+    const uint32_t o = p.own_begin + i;
+    const float2 pr = predict_position(p, ps, vs);
+    pos_s[o] = ps;
+    vel_s[o] = vs;
+    pred_s[o] = pr;
+    keys_ext[o] = k;
     if (!(tame_component(pr.x) && tame_component(pr.y) && tame_component(vs.x) && tame_component(vs.y))) *wild_stamp = __ldg(frame_time);
 }
 __device__ __forceinline__ void stamp_if_wild(float2 pr, float2 vs, uint32_t* wild_stamp, const uint32_t* frame_time) {

@@ -80,6 +80,9 @@ struct Sim {
     uint32_t emig_cap = 0;
     uint32_t* slab_meta = nullptr;
     DevParams slab_params{};
+    uint32_t* slab_bin_lb = nullptr;          // counting sort of a band: exclusive scan over its cells + the sentinel bin
+    uint32_t slab_bins = 0, slab_bin_tiles = 0;
+    bool slab_counting = true;                // FLUID_SLAB_RADIX=1: radix passes always
     uint32_t* slab_dyn = nullptr;             // SlabDyn (kernels_slab.cuh), device-resolved protocol
     const uint32_t* slab_goff_dev = nullptr;  // &slab_dyn->global_offset while that protocol is in use, else null
 

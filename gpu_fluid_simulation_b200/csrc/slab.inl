@@ -56,6 +56,17 @@ int fluid_slab_configure(FluidSim* h, int rank, int world, const uint32_t* row_b
     FLUID_CUDA(cudaMalloc(&s->emig_list, (size_t)emig_cap * 8));
     FLUID_CUDA(cudaMalloc(&s->slab_meta, 256));
     FLUID_CUDA(cudaMemsetAsync(s->slab_meta, 0, 256, s->stream));
+    {
+        // counting sort of the band (kernels_count.cuh): bins = the band's cells + one for the sentinel key of emigrants
+        const uint32_t band_rows = row_bounds[rank + 1] - row_bounds[rank];
+        s->slab_bins = band_rows * s->grid_w + 1u;
+        s->slab_bin_tiles = (uint32_t)(((size_t)s->slab_bins + CELL_SCAN_TILE - 1) / CELL_SCAN_TILE);  // <= cell_tiles: the arrays of the whole grid hold it
+        if (s->slab_bin_lb) cudaFree(s->slab_bin_lb);
+        FLUID_CUDA(cudaMalloc(&s->slab_bin_lb, (size_t)s->slab_bin_tiles * CELL_SCAN_TILE * 4));
+        const char* radix = getenv("FLUID_SLAB_RADIX");
+        s->slab_counting = !(radix && radix[0] == '1');
+        s->cell_max_known = false;
+    }
     if (!s->slab_dyn) FLUID_CUDA(cudaMalloc(&s->slab_dyn, 64));
     FLUID_CUDA(cudaMemsetAsync(s->slab_dyn, 0, 64, s->stream));
     s->emig_count = s->slab_meta + 8;  // meta words 0..4, emigrant counter at word 8, per-destination counters at words 16..31
@@ -166,41 +177,82 @@ int fluid_slab_sort(FluidSim* h, uint32_t n_from_below, uint32_t n_from_above, u
     DevParams& p = s->slab_params;
     slab_hash(s, p, begin, n_from_below, 0, nullptr);
     slab_hash(s, p, s->state_off + s->n, n_from_above, 0, nullptr);
-    const uint32_t passes = s->sort_passes;
-    uint32_t* hist = s->sort_scratch;
-    uint32_t* counters = s->sort_scratch + MAX_PASSES * RADIX;
-    uint32_t* status = counters + RADIX;
-    k_scan_histograms<<<passes, RADIX, 0, s->stream>>>(hist);
-    s->launches++;
-    const uint32_t tiles = (total + SORT_TILE - 1) / SORT_TILE;
-    const size_t sort_smem = (size_t)SORT_TILE * 2 * sizeof(uint32_t);
-    const uint32_t* kin = s->keys_u + begin;
-    const uint32_t* vin = nullptr;
-    uint32_t* kout = s->keys_b;
-    uint32_t* vout = s->idx_a;
-    for (uint32_t q = 0; q < passes && tiles > 0; q++) {
-        if (q == 0)
-            k_onesweep_pass<SORT_ITEMS, true><<<tiles, SORT_THREADS, sort_smem, s->stream>>>(
-                kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, total, (int)(q * RADIX_BITS));
-        else
-            k_onesweep_pass<SORT_ITEMS, false><<<tiles, SORT_THREADS, sort_smem, s->stream>>>(
-                kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, total, (int)(q * RADIX_BITS));
-        s->launches++;
-        kin = kout; vin = vout;
-        kout = (kout == s->keys_b) ? s->keys_c : s->keys_b;
-        vout = (vout == s->idx_a) ? s->idx_b : s->idx_a;
+    // key order: counting sort over the band's cells (same stable order as the radix passes, kernels_count.cuh) unless
+    // the cells are crowded. The statistics come from the previous tick's scan (the protocol's host read of the
+    // migration counts has synchronised the stream since); the first tick after configure / a resize takes the radix
+    // passes and only gathers the statistics.
+    const uint32_t key_lo = s->slab_rows.bounds[s->slab_rows.rank] * s->grid_w;
+    const uint32_t last_bin = s->slab_bins - 1u;
+    bool counting = false;
+    if (s->slab_counting && total > 0) {
+        uint32_t* count = s->cell_count_buf[0];
+        const size_t bin_bytes = (size_t)s->slab_bin_tiles * CELL_SCAN_TILE * 4;
+        FLUID_CUDA(cudaMemsetAsync(count, 0, bin_bytes, s->stream));
+        k_count_keys<<<(total + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(s->keys_u + begin, total, key_lo, last_bin, count);
+        if (s->cell_max_known) {
+            const uint32_t max_ok = std::min(std::max(total / 1024u, COUNT_SORT_MAX_CELL_LO), COUNT_SORT_MAX_CELL_HI);
+            const uint32_t sq_bits = s->cell_max_host[1];
+            float sum_sq;
+            memcpy(&sum_sq, &sq_bits, 4);
+            counting = s->cell_max_host[0] <= max_ok && sum_sq <= COUNT_SORT_MAX_MEAN_SQ * (float)total;
+        }
+        k_cell_reduce<<<s->slab_bin_tiles, CELL_SCAN_THREADS, 0, s->stream>>>(count, s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq);
+        k_cell_downsweep<<<s->slab_bin_tiles, CELL_SCAN_THREADS, 0, s->stream>>>(count, s->slab_bin_lb, s->cell_tile_sum, s->cell_tile_max,
+                                                                               s->cell_tile_sq, s->slab_bin_tiles, s->cell_max_dev,
+                                                                               s->cell_count_buf[1]);
+        s->launches += 3;
+        s->cell_max_known = true;
     }
-    s->keys_sorted = const_cast<uint32_t*>(kin);
-    s->idx_sorted = const_cast<uint32_t*>(vin);
-    s->mark("sort");
-    s->n = total - n_emigrants;  // sentinel keys sorted to the tail and are dropped here
+    s->n = total - n_emigrants;  // sentinel keys sort to the tail and are dropped here
     p.n = s->n;
     p.own_begin = s->sorted_off;
-    if (s->n) {
-        k_slab_gather<<<(s->n + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
-            p, s->keys_sorted, s->idx_sorted, s->pos_a + begin, s->vel_a + begin, s->pos_s, s->pred_s, s->vel_s, s->keys_ext,
-            s->quirk + 2, s->d_frame_time);
+    if (counting) {
+        k_cell_slots<<<(total + GATHER_THREADS * SLOT_ITEMS - 1) / (GATHER_THREADS * SLOT_ITEMS), GATHER_THREADS, 0, s->stream>>>(
+            total, key_lo, last_bin, s->keys_u + begin, s->cell_count_buf[0], s->keys_b, s->idx_a);
         s->launches++;
+        s->keys_sorted = s->keys_b;
+        s->idx_sorted = nullptr;
+        s->mark("sort");
+        k_slab_rank_gather<<<(total + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
+            p, total, key_lo, last_bin, s->keys_b, s->idx_a, s->slab_bin_lb, s->pos_a + begin, s->vel_a + begin, s->pos_s, s->pred_s,
+            s->vel_s, s->keys_ext, s->quirk + 2, s->d_frame_time);
+        s->launches++;
+        s->last_sort_path = FLUID_SORT_COUNTING;
+    } else {
+        const uint32_t passes = s->sort_passes;
+        uint32_t* hist = s->sort_scratch;
+        uint32_t* counters = s->sort_scratch + MAX_PASSES * RADIX;
+        uint32_t* status = counters + RADIX;
+        k_scan_histograms<<<passes, RADIX, 0, s->stream>>>(hist);
+        s->launches++;
+        const uint32_t tiles = (total + SORT_TILE - 1) / SORT_TILE;
+        const size_t sort_smem = (size_t)SORT_TILE * 2 * sizeof(uint32_t);
+        const uint32_t* kin = s->keys_u + begin;
+        const uint32_t* vin = nullptr;
+        uint32_t* kout = s->keys_b;
+        uint32_t* vout = s->idx_a;
+        for (uint32_t q = 0; q < passes && tiles > 0; q++) {
+            if (q == 0)
+                k_onesweep_pass<SORT_ITEMS, true><<<tiles, SORT_THREADS, sort_smem, s->stream>>>(
+                    kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, total, (int)(q * RADIX_BITS));
+            else
+                k_onesweep_pass<SORT_ITEMS, false><<<tiles, SORT_THREADS, sort_smem, s->stream>>>(
+                    kin, vin, kout, vout, hist + q * RADIX, counters + q, status + (size_t)q * tiles * RADIX, total, (int)(q * RADIX_BITS));
+            s->launches++;
+            kin = kout; vin = vout;
+            kout = (kout == s->keys_b) ? s->keys_c : s->keys_b;
+            vout = (vout == s->idx_a) ? s->idx_b : s->idx_a;
+        }
+        s->keys_sorted = const_cast<uint32_t*>(kin);
+        s->idx_sorted = const_cast<uint32_t*>(vin);
+        s->mark("sort");
+        if (s->n) {
+            k_slab_gather<<<(s->n + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
+                p, s->keys_sorted, s->idx_sorted, s->pos_a + begin, s->vel_a + begin, s->pos_s, s->pred_s, s->vel_s, s->keys_ext,
+                s->quirk + 2, s->d_frame_time);
+            s->launches++;
+        }
+        s->last_sort_path = FLUID_SORT_RADIX;
     }
     const uint32_t row_first = s->slab_rows.bounds[s->slab_rows.rank], row_end = s->slab_rows.bounds[s->slab_rows.rank + 1];
     k_slab_meta<<<1, 32, 0, s->stream>>>(s->keys_ext + s->sorted_off, s->n, s->grid_w, row_first, row_end > row_first ? row_end - 1 : row_first,
