@@ -253,10 +253,12 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     const uint32_t gblocks = (n + GATHER_THREADS - 1) / GATHER_THREADS;
     const bool counted = sort_mode != FLUID_SORT_RADIX;
     bool counting = false;
+    uint32_t* cursor = nullptr;
     if (counted) {
         // the two count arrays alternate: this tick's was cleared by the previous counted tick's scan (or at create)
         cell_count = cell_count_buf[cell_count_cur];
         uint32_t* const count_next = cell_count_buf[cell_count_cur ^ 1];
+        cursor = cell_count;  // the two-kernel scan turns the counts into the cursors in place
         cell_count_cur ^= 1;
         const uint32_t pairs = (n + 1) / 2;
         uint32_t blocks = (pairs + HASH_THREADS - 1) / HASH_THREADS;
@@ -265,10 +267,17 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
         launch_pdl(pdl, k_predict_key_count, dim3(blocks), dim3(HASH_THREADS), stream, p, pos_a, vel_a, keys_u, cell_count, d_frame_time);
         launches++;
         mark("predict+key+hist");
-        launch_pdl(pdl, k_cell_reduce, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_tile_sum, cell_tile_max, cell_tile_sq);
-        launch_pdl(pdl, k_cell_downsweep, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_lb, cell_tile_sum,
-                   cell_tile_max, cell_tile_sq, cell_tiles, cell_max_dev, count_next);
-        launches += 2;
+        if (cell_tiles <= CELL_SCAN_SMALL_MAX_TILES) {
+            launch_pdl(pdl, k_cell_scan_small, dim3(cell_tiles), dim3(CELL_SCAN_SMALL_THREADS), stream, cell_count, cell_cursor,
+                       cell_lb, cell_max_dev, count_next);
+            launches += 1;
+            cursor = cell_cursor;
+        } else {
+            launch_pdl(pdl, k_cell_reduce, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_tile_sum, cell_tile_max, cell_tile_sq);
+            launch_pdl(pdl, k_cell_downsweep, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_lb, cell_tile_sum,
+                       cell_tile_max, cell_tile_sq, cell_tiles, cell_max_dev, count_next);
+            launches += 2;
+        }
         if (sort_mode == FLUID_SORT_COUNTING) {
             counting = true;
         } else {
@@ -286,7 +295,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     }
     if (counting) {
         launch_pdl(pdl, k_cell_slots, dim3((n + GATHER_THREADS * SLOT_ITEMS - 1) / (GATHER_THREADS * SLOT_ITEMS)), dim3(GATHER_THREADS),
-                   stream, n, 0u, p.num_cells - 1u, keys_u, cell_count, keys_b, idx_a);
+                   stream, n, 0u, p.num_cells - 1u, keys_u, cursor, keys_b, idx_a);
         launches++;
         mark("sort");
         launch_pdl(pdl, k_rank_gather_cells, dim3((n + GATHER_THREADS * RANK_ITEMS - 1) / (GATHER_THREADS * RANK_ITEMS)),
@@ -424,6 +433,7 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
         cudaMalloc(&sim->cell_lb, cells_padded * 4) != cudaSuccess ||
         cudaMalloc(&sim->cell_count_buf[0], cells_padded * 4) != cudaSuccess ||
         cudaMalloc(&sim->cell_count_buf[1], cells_padded * 4) != cudaSuccess ||
+        (sim->cell_tiles <= CELL_SCAN_SMALL_MAX_TILES && cudaMalloc(&sim->cell_cursor, cells_padded * 4) != cudaSuccess) ||
         cudaMalloc(&sim->cell_tile_sum, (size_t)sim->cell_tiles * 4) != cudaSuccess ||
         cudaMalloc(&sim->cell_tile_max, (size_t)sim->cell_tiles * 4) != cudaSuccess ||
         cudaMalloc(&sim->cell_tile_sq, (size_t)sim->cell_tiles * 4) != cudaSuccess ||
@@ -484,7 +494,7 @@ void fluid_sim_destroy(FluidSim* h) {
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
                     s->idx_b, s->sort_scratch, s->tile_plans, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
                     s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta,
-                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq, s->slab_bin_lb};
+                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq, s->slab_bin_lb, s->cell_cursor};
     for (void* b : bufs) if (b) cudaFree(b);
     if (s->cell_max_host) cudaFreeHost((void*)s->cell_max_host);
     if (s->h2d_stream) { cudaStreamSynchronize(s->h2d_stream); cudaStreamDestroy(s->h2d_stream); }

@@ -207,6 +207,74 @@ k_cell_downsweep(uint32_t* __restrict__ count_cursor, uint32_t* __restrict__ cel
     }
 }
 
+// Small grids (the reference's default scene has 71,289 cells = 18 tiles): the scan in ONE launch — at this size a kernel
+// boundary (~4 us) costs more than the work. CTA b owns tile b (4096 cells, one uint4 per thread) and gets its base by
+// summing the raw counts of the tiles before it itself (at most 31 coalesced uint4 loads per thread, all L2 hits), so no
+// CTA waits for another. The counts are therefore read-only here and the cursors go to their own array. The last CTA
+// has seen every cell and publishes the statistics. Same cell_lb / cursors / statistics as k_cell_reduce + k_cell_downsweep.
+constexpr int CELL_SCAN_SMALL_THREADS = 1024;
+constexpr uint32_t CELL_SCAN_SMALL_MAX_TILES = 32;
+static_assert(CELL_SCAN_SMALL_THREADS * 4 == CELL_SCAN_TILE, "one uint4 per thread per tile");
+__global__ void __launch_bounds__(CELL_SCAN_SMALL_THREADS)
+k_cell_scan_small(const uint32_t* __restrict__ count, uint32_t* __restrict__ cursor, uint32_t* __restrict__ cell_lb,
+                  volatile uint32_t* __restrict__ host_max, uint32_t* __restrict__ zero_next) {
+    pdl_enter();
+    __shared__ uint32_t s_pre[32], s_own[32], s_max[32];
+    __shared__ float s_sq[32];
+    const uint32_t t = threadIdx.x, lane = lane_id(), warp = t >> 5, b = blockIdx.x;
+    const uint4* all = reinterpret_cast<const uint4*>(count);
+    uint32_t pre = 0, mx = 0;
+    float sq = 0.0f;
+#pragma unroll 8
+    for (uint32_t k = 0; k < b; k++) {
+        const uint4 v = __ldg(all + (size_t)k * CELL_SCAN_SMALL_THREADS + t);
+        pre += v.x + v.y + v.z + v.w;
+        mx = max(max(mx, max(v.x, v.y)), max(v.z, v.w));
+        sq += (float)v.x * (float)v.x + (float)v.y * (float)v.y + (float)v.z * (float)v.z + (float)v.w * (float)v.w;
+    }
+    const size_t mine = (size_t)b * CELL_SCAN_SMALL_THREADS + t;
+    const uint4 v = __ldg(all + mine);
+    const uint32_t own = v.x + v.y + v.z + v.w;
+    mx = max(max(mx, max(v.x, v.y)), max(v.z, v.w));
+    sq += (float)v.x * (float)v.x + (float)v.y * (float)v.y + (float)v.z * (float)v.z + (float)v.w * (float)v.w;
+    uint32_t incl = own;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= (uint32_t)o) incl += u;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        pre += __shfl_xor_sync(0xffffffffu, pre, o);
+        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    }
+    if (lane == 31) s_own[warp] = incl;
+    if (lane == 0) { s_pre[warp] = pre; s_max[warp] = mx; s_sq[warp] = sq; }
+    __syncthreads();
+    uint32_t run = incl - own;
+#pragma unroll
+    for (int w = 0; w < CELL_SCAN_SMALL_THREADS / 32; w++) {
+        run += s_pre[w];
+        if ((uint32_t)w < warp) run += s_own[w];
+    }
+    uint4 o;
+    o.x = run; run += v.x;
+    o.y = run; run += v.y;
+    o.z = run; run += v.z;
+    o.w = run;
+    reinterpret_cast<uint4*>(cursor)[mine] = o;
+    reinterpret_cast<uint4*>(cell_lb)[mine] = o;
+    reinterpret_cast<uint4*>(zero_next)[mine] = make_uint4(0u, 0u, 0u, 0u);
+    if (b == gridDim.x - 1u && t == 0) {
+        uint32_t m = 0;
+        float q = 0.0f;
+        for (int w = 0; w < CELL_SCAN_SMALL_THREADS / 32; w++) { m = max(m, s_max[w]); q += s_sq[w]; }
+        host_max[0] = m;
+        host_max[1] = __float_as_uint(q);
+    }
+}
+
 // slot = cursor[cell]++, one atomic per run of equal cells along the lanes; the run's lanes take consecutive slots, so a
 // cell's block is a concatenation of runs that are each in source order (k_rank_gather_cells orders the runs).
 // A warp takes SLOT_ITEMS rows of 32 consecutive particles and issues the rows' loads, then their atomics, back to back:

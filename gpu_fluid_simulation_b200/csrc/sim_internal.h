@@ -45,6 +45,7 @@ struct Sim {
     uint32_t* cell_count = nullptr;              // the array the current tick counts into (one of the two below)
     uint32_t* cell_count_buf[2] = {nullptr, nullptr};  // alternate per counted tick; the scan clears the other one
     int cell_count_cur = 0;
+    uint32_t* cell_cursor = nullptr;             // small grids (k_cell_scan_small): the cursors live apart from the counts
     bool pdl = true;                             // programmatic dependent launch on the tick's kernels (FLUID_NO_PDL=1: off)
     uint32_t *cell_tile_sum = nullptr, *cell_tile_max = nullptr;
     float* cell_tile_sq = nullptr;

@@ -126,7 +126,8 @@ void fluid_sim_destroy(FluidSim* sim);
  * Asynchronous, mirroring the reference's record-then-submit (src/main.rs:226). */
 int fluid_sim_tick(FluidSim* sim, const FluidTickSettings* tick);
 /* `n` consecutive ticks with the same settings (reference: the Running/Render loops,
- * src/main.rs:137-147,199-201), replayed from a captured CUDA graph. */
+ * src/main.rs:137-147,199-201), enqueued back to back from one call (eight kernels per tick, chained by programmatic
+ * dependent launch; no host synchronisation in between except the first tick after an upload). */
 int fluid_sim_tick_n(FluidSim* sim, const FluidTickSettings* tick, uint32_t n);
 /* reference: `device.poll(Wait)`, src/main.rs:79. */
 int fluid_sim_sync(FluidSim* sim);

@@ -245,6 +245,36 @@ def test_golden_fixtures(fluid, name):
             assert np.array_equal(got[f], ref[f]), f  # and in fact identical
 
 
+def test_config1_default_scene_100_frames(fluid, oracle):
+    """BASELINE.json config 1: the reference's default scene (src/main.rs:48-54: 100,000 particles on the init lattice of
+    src/simulation.rs:147-163, 72 coincident pairs) stepped for 100 frames with the default tick settings
+    (src/renderer.rs:374-388). (a) The whole trajectory: every step is bit-identical, so the states after 1, 50 and 100
+    frames are too. (b) Per-step parity from the oracle's own states at ticks 1, 50 and 100 (identical input state ->
+    one tick), all criteria of parity.compare_state."""
+    s, ts = SimulationSettings(), TickSettings()
+    osim = oracle.OracleSim(s, oracle.init_lattice(s))
+    snaps = {}
+    with fluid.FluidSimulation.new(0, s) as sim:  # create() builds the same lattice
+        for t in range(1, 101):
+            if t in (1, 50, 100):
+                snaps[t] = (osim.p.copy(), osim.table.copy())
+            osim.tick(ts)
+            sim.tick(ts)
+            if t in (1, 50, 100):
+                got = sim.download_particles()
+                assert np.array_equal(sim.download_start_indices(), osim.table), t
+                for f in ("grid", "position", "predicted_position", "velocity", "density"):
+                    assert np.array_equal(got[f], osim.p[f]), (t, f)
+        assert sim.tick_count == 100
+    for t, (state, table) in snaps.items():
+        o2, s2, extras = parity.run_pair(fluid, oracle, s, ts, state, table=table, tick_count=t - 1)
+        try:
+            stats = parity.compare_state(o2, s2, extras, ts)
+            assert stats["floats_bit_exact"], (t, stats)
+        finally:
+            s2.close()
+
+
 def test_config2_hash_sort_table_1m_bit_exact(fluid, oracle):
     """BASELINE.json config 2: spatial hash + key sort + cell-start table, 1M particles, bit-exact."""
     for s, ts, p in (scenes.uniform_box(1000), scenes.dam_break(500, 2000)):
