@@ -237,6 +237,8 @@ def main():
         sim.tick_n(ts, args.steps)
         sim.sync()
     phases = sim.last_timing()
+    between_ticks_ms = dict(phases).get("between ticks")  # device idle between two ticks (0 while the host keeps up)
+    phases = [(k_, v) for k_, v in phases if k_ in ALGO_BYTES]
     sort_path = "counting" if sim.last_sort_path == 2 else "radix"
     launches = launches_timed
     clock_window = "timed region"
@@ -270,6 +272,7 @@ def main():
                                "achieved": ALGO_BYTES_TOTAL * n / (ms_per_step * 1e-3) / 1e9,
                                "frac": ALGO_BYTES_TOTAL * n / (ms_per_step * 1e-3) / 1e9 / peak},
                 "phases_ms": {k: round(v, 5) for k, v in phases},
+                "between_ticks_ms": None if between_ticks_ms is None else round(between_ticks_ms, 5),
                 "phases_source": "events inside the timed region" if marks_in_region else
                                  "second pass of the same K steps with per-phase events (the timed region runs without them)",
                 "phase_frac_of_peak": {k: round(ALGO_BYTES[k] * n / (v * 1e-3) / 1e9 / peak, 4) for k, v in phases if v > 0}}

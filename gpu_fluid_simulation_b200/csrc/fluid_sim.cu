@@ -755,6 +755,20 @@ int fluid_sim_last_timing(FluidSim* h, const char** names, float* ms, int cap) {
         if (names) names[out] = s->mark_names[k];
         if (ms) ms[out] = (float)(sum / (double)ticks);
     }
+    // device time between the last mark of a tick and the first mark of the next one: zero while the host keeps the
+    // stream fed, the host's lag otherwise (slab mode: everything the driver does between two ticks)
+    if (ticks >= 2 && out < cap && s->marks_per_tick >= 2) {
+        double sum = 0.0;
+        for (uint64_t t = 0; t + 1 < ticks; t++) {
+            const uint64_t later = (s->timed_ticks - 1 - t) % TIMING_RING, earlier = (s->timed_ticks - 2 - t) % TIMING_RING;
+            float dt = 0.f;
+            FLUID_CUDA(cudaEventElapsedTime(&dt, s->mark_events[earlier][s->marks_per_tick - 1], s->mark_events[later][0]));
+            sum += dt;
+        }
+        if (names) names[out] = "between ticks";
+        if (ms) ms[out] = (float)(sum / (double)(ticks - 1));
+        out++;
+    }
     return out;
 }
 uint64_t fluid_sim_launch_count(const FluidSim* h) { return h ? reinterpret_cast<const Sim*>(h)->launches : 0; }

@@ -507,13 +507,19 @@ def run_slab_bench(args, rank, world, local_rank, workloads, algo_bytes, peak, p
     for _ in range(args.warmup):
         drv.tick(ts)
     r.sync()
-    dist.barrier()
-    torch.cuda.synchronize()
+    # the clock sampler (an nvidia-smi subprocess on rank 0) starts BEFORE the barrier: started after it, its start-up
+    # (tens of ms on some hosts) delayed rank 0's first collective while the other ranks' start events were already
+    # recorded, and the max over ranks charged that skew to the timed region (3 ms per step at 20 steps)
     sampler = sampler_cls(local_rank)
     if rank == 0:
         sampler.start()
-    launches0 = r.sim.launch_count
     r.sim.enable_timing(True)
+    drv.tick(ts)  # one more untimed tick with the event marks on (creates the events of the first ring slot)
+    r.sync()
+    dist.barrier()
+    torch.cuda.synchronize()
+    dist.barrier()
+    launches0 = r.sim.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(r.stream)
     for _ in range(args.steps):
