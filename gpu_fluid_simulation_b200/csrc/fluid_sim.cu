@@ -219,14 +219,15 @@ void launch_tile_plans(Sim* s, const DevParams& p, const uint32_t* keys, bool pd
     s->launches++;
 }
 
-void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, float2* vel_out, bool pdl = false) {
+void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, float2* vel_out, bool pdl = false,
+                  uint32_t* next_keys = nullptr, uint32_t* next_count = nullptr) {
     float2* da = s->debug_force ? s->dbg_accel : nullptr;
     float2* db = s->debug_force ? s->dbg_abs : nullptr;
     const uint32_t* keys = s->slab ? s->keys_ext : s->keys_sorted;
 #define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                     \
     launch_pdl(pdl, k_force_integrate<DBG, EX>, dim3(blocks), dim3(SPH_THREADS), s->stream, p, s->pos_s, s->pred_s, s->vel_s, \
                s->rho, keys, s->cell_lb, s->quirk, s->force_field, s->d_frame_time, s->slab_goff_dev, s->quirk + 2,     \
-               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db)
+               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db, next_keys, next_count)
     if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
     else { if (s->exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
 #undef FLUID_LAUNCH_FORCE
@@ -254,26 +255,40 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     const bool counted = sort_mode != FLUID_SORT_RADIX;
     bool counting = false;
     uint32_t* cursor = nullptr;
+    uint32_t* count_next = nullptr;
+    uint32_t bump_in_scan = 0u;
+    const bool had_spec = spec_valid;
+    spec_valid = false;  // consumed or dropped by this tick; set again below if this tick's force pass speculates
     if (counted) {
         // the two count arrays alternate: this tick's was cleared by the previous counted tick's scan (or at create)
         cell_count = cell_count_buf[cell_count_cur];
-        uint32_t* const count_next = cell_count_buf[cell_count_cur ^ 1];
+        count_next = cell_count_buf[cell_count_cur ^ 1];
         cursor = cell_count;  // the two-kernel scan turns the counts into the cursors in place
         cell_count_cur ^= 1;
-        const uint32_t pairs = (n + 1) / 2;
-        uint32_t blocks = (pairs + HASH_THREADS - 1) / HASH_THREADS;
-        const uint32_t max_blocks = (uint32_t)num_sms * 8u;
-        if (blocks > max_blocks) blocks = max_blocks;
-        launch_pdl(pdl, k_predict_key_count, dim3(blocks), dim3(HASH_THREADS), stream, p, pos_a, vel_a, keys_u, cell_count, d_frame_time);
-        launches++;
+        // did the previous tick's force pass already emit this tick's keys and counts (same delta, state untouched)?
+        const bool hit = had_spec && memcmp(&spec_delta, &t.delta, sizeof(float)) == 0;
+        if (hit) {
+            std::swap(keys_u, keys_c);  // the speculative keys become this tick's unsorted keys
+            bump_in_scan = 1u;
+        } else {
+            if (count_dirty) FLUID_CUDA(cudaMemsetAsync(cell_count, 0, (size_t)cell_tiles * CELL_SCAN_TILE * 4, stream));  // unused speculation
+            const uint32_t pairs = (n + 1) / 2;
+            uint32_t blocks = (pairs + HASH_THREADS - 1) / HASH_THREADS;
+            const uint32_t max_blocks = (uint32_t)num_sms * 8u;
+            if (blocks > max_blocks) blocks = max_blocks;
+            launch_pdl(pdl, k_predict_key_count, dim3(blocks), dim3(HASH_THREADS), stream, p, pos_a, vel_a, keys_u, cell_count, d_frame_time);
+            launches++;
+        }
+        count_dirty = false;
         mark("predict+key+hist");
         if (cell_tiles <= CELL_SCAN_SMALL_MAX_TILES) {
             launch_pdl(pdl, k_cell_scan_small, dim3(cell_tiles), dim3(CELL_SCAN_SMALL_THREADS), stream, cell_count, cell_cursor,
-                       cell_lb, cell_max_dev, count_next);
+                       cell_lb, cell_max_dev, count_next, d_frame_time, bump_in_scan);
             launches += 1;
             cursor = cell_cursor;
         } else {
-            launch_pdl(pdl, k_cell_reduce, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_tile_sum, cell_tile_max, cell_tile_sq);
+            launch_pdl(pdl, k_cell_reduce, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_tile_sum, cell_tile_max, cell_tile_sq,
+                       d_frame_time, bump_in_scan);
             launch_pdl(pdl, k_cell_downsweep, dim3(cell_tiles), dim3(CELL_SCAN_THREADS), stream, cell_count, cell_lb, cell_tile_sum,
                        cell_tile_max, cell_tile_sq, cell_tiles, cell_max_dev, count_next);
             launches += 2;
@@ -368,7 +383,11 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
                d_frame_time, reinterpret_cast<const TilePlan*>(tile_plans));
     launches++;
     mark("density");
-    launch_force(this, p, sblocks, pos_a, vel_a, pdl);
+    // the force pass emits the next tick's keys (into keys_c: free on the counting path, and the radix passes of THIS tick are
+    // done with it by now) and counts (into the count array the next counted tick will use, cleared by this tick's scan)
+    const bool spec = speculate && counted && count_next != nullptr && keys_sorted != keys_c;  // (radix passes of an even count end in keys_c)
+    launch_force(this, p, sblocks, pos_a, vel_a, pdl, spec ? keys_c : nullptr, spec ? count_next : nullptr);
+    if (spec) { spec_valid = true; count_dirty = true; spec_delta = t.delta; }
     mark("force+integrate");
     if (timing) { marks_per_tick = n_marks; timed_ticks++; }
     FLUID_CUDA(cudaGetLastError());
@@ -452,6 +471,8 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
     {
         const char* no_pdl = getenv("FLUID_NO_PDL");
         sim->pdl = !(no_pdl && no_pdl[0] == '1');
+        const char* no_spec = getenv("FLUID_NO_SPECULATION");
+        sim->speculate = !(no_spec && no_spec[0] == '1');
     }
     cudaMemsetAsync(sim->quirk, 0, 16, sim->stream);
     cudaMemsetAsync(sim->d_frame_time, 0, 4, sim->stream);
@@ -580,6 +601,7 @@ int fluid_sim_upload_particles(FluidSim* h, const FluidParticle* src) {
     if (rc != FLUID_OK) return rc;
     FLUID_CUDA(cudaMemcpyAsync(s->aos_stage, src, (size_t)s->n * sizeof(FluidParticle), cudaMemcpyHostToDevice, s->stream));
     s->cell_max_known = false;
+    s->spec_valid = false;
     if (s->n == 0) return FLUID_OK;
     k_aos_to_soa<<<(s->n + 255) / 256, 256, 0, s->stream>>>(s->aos_stage, s->n, s->pos_a + s->state_off, s->pred_s + s->sorted_off,
                                                           s->vel_a + s->state_off, s->rho + s->sorted_off, s->keys_view());
@@ -619,6 +641,7 @@ int fluid_sim_upload_particles_async(FluidSim* h, const FluidParticle* src) {
     FLUID_CUDA(cudaEventRecord(s->ev_in_free, s->stream));
     s->in_used = true;
     s->cell_max_known = false;
+    s->spec_valid = false;
     FLUID_CUDA(cudaGetLastError());
     return FLUID_OK;
 }
@@ -789,6 +812,8 @@ int fluid_sim_set_sort_mode(FluidSim* h, int mode) {
         return invalid("fluid_sim_set_sort_mode: unknown mode");
     s->sort_mode = mode;
     s->cell_max_known = false;
+    s->spec_valid = false;
+    s->count_dirty = false;
     // both count arrays clean again, whatever ran before (ticks in FLUID_SORT_RADIX mode do not touch them)
     const size_t bytes = (size_t)s->cell_tiles * CELL_SCAN_TILE * 4;
     FLUID_CUDA(cudaMemsetAsync(s->cell_count_buf[0], 0, bytes, s->stream));
@@ -832,6 +857,7 @@ int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
     cudaFree(pa); cudaFree(va); cudaFree(pr); cudaFree(rh); cudaFree(ks);
     s->idx_sorted = nullptr;
     s->cell_max_known = false;
+    s->spec_valid = false;
     if (dbg) return fluid_sim_enable_debug_force(h, 1);
     return FLUID_OK;
 }
@@ -846,6 +872,7 @@ int fluid_sim_set_particle_count(FluidSim* h, uint32_t n) {
     if (n < 2 || n > s->capacity) return invalid("fluid_sim_set_particle_count: need 2 <= n <= capacity");
     s->n = n;
     s->cell_max_known = false;
+    s->spec_valid = false;
     return FLUID_OK;
 }
 

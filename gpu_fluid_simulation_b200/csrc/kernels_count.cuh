@@ -43,15 +43,7 @@ __device__ __forceinline__ uint32_t count_bin(uint32_t key, uint32_t key_lo, uin
 
 // count[cell] += 1 for every valid lane; the first lane of every run of equal cells adds the run's length
 __device__ __forceinline__ void cell_count_add(uint32_t* __restrict__ count, uint32_t cell, bool valid) {
-    const uint32_t lane = lane_id();
-    const uint32_t d = valid ? cell : 0xffffffffu;
-    const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
-    const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0u || d != prev);
-    if (valid && ((heads >> lane) & 1u)) {
-        const uint32_t above = heads & ~((2u << lane) - 1u);  // run heads in the lanes above this one
-        const uint32_t next = above ? (uint32_t)__ffs(above) - 1u : 32u;
-        atomicAdd(count + cell, next - lane);
-    }
+    atomic_count_run(count, cell, valid);
 }
 
 // K1+K2 as in k_predict_key_hist (same arithmetic, same bits), with the per-cell count in place of the digit histograms
@@ -111,8 +103,10 @@ __device__ __forceinline__ uint32_t block_max_256(uint32_t v, uint32_t* s_tmp /*
 // per tile of CELL_SCAN_TILE cells: particle count and largest cell (the count array is zero-padded to whole tiles)
 __global__ void __launch_bounds__(CELL_SCAN_THREADS)
 k_cell_reduce(const uint32_t* __restrict__ count, uint32_t* __restrict__ tile_sum, uint32_t* __restrict__ tile_max,
-              float* __restrict__ tile_sq) {
+              float* __restrict__ tile_sq, uint32_t* __restrict__ frame_time, uint32_t bump) {
     pdl_enter();
+    // first kernel of a tick whose keys and counts came from the previous tick's force pass: self.tick += 1 (src/simulation.rs:460)
+    if (bump && blockIdx.x == 0 && threadIdx.x == 0) *frame_time += bump;
     __shared__ uint32_t s_tmp[CELL_SCAN_THREADS / 32];
     __shared__ float s_sq[CELL_SCAN_THREADS / 32];
     const uint4* src = reinterpret_cast<const uint4*>(count + (size_t)blockIdx.x * CELL_SCAN_TILE) + threadIdx.x * (CELL_SCAN_ITEMS / 4);
@@ -217,8 +211,10 @@ constexpr uint32_t CELL_SCAN_SMALL_MAX_TILES = 32;
 static_assert(CELL_SCAN_SMALL_THREADS * 4 == CELL_SCAN_TILE, "one uint4 per thread per tile");
 __global__ void __launch_bounds__(CELL_SCAN_SMALL_THREADS)
 k_cell_scan_small(const uint32_t* __restrict__ count, uint32_t* __restrict__ cursor, uint32_t* __restrict__ cell_lb,
-                  volatile uint32_t* __restrict__ host_max, uint32_t* __restrict__ zero_next) {
+                  volatile uint32_t* __restrict__ host_max, uint32_t* __restrict__ zero_next,
+                  uint32_t* __restrict__ frame_time, uint32_t bump) {
     pdl_enter();
+    if (bump && blockIdx.x == 0 && threadIdx.x == 0) *frame_time += bump;  // as in k_cell_reduce
     __shared__ uint32_t s_pre[32], s_own[32], s_max[32];
     __shared__ float s_sq[32];
     const uint32_t t = threadIdx.x, lane = lane_id(), warp = t >> 5, b = blockIdx.x;

@@ -347,6 +347,20 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
     }
 }
 
+// count[cell] += 1 for every valid lane, one atomic per run of equal cells along the lanes (kernels_count.cuh
+// cell_count_add is this function; it lives here because the force pass uses it too)
+__device__ __forceinline__ void atomic_count_run(uint32_t* __restrict__ count, uint32_t cell, bool valid) {
+    const uint32_t lane = lane_id();
+    const uint32_t d = valid ? cell : 0xffffffffu;
+    const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
+    const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0u || d != prev);
+    if (valid && ((heads >> lane) & 1u)) {
+        const uint32_t above = heads & ~((2u << lane) - 1u);  // run heads in the lanes above this one
+        const uint32_t next = above ? (uint32_t)__ffs(above) - 1u : 32u;
+        atomicAdd(count + cell, next - lane);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // K6 force + integrate
 // ------------------------------------------------------------------------------------------------
@@ -824,7 +838,8 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
                   const uint32_t* __restrict__ wild_stamp /* null: always take the per-pair range tests */,
                   const TilePlan* __restrict__ plans,
                   float2* __restrict__ pos_out, float2* __restrict__ vel_out, float2* __restrict__ dbg_accel,
-                  float2* __restrict__ dbg_abs) {
+                  float2* __restrict__ dbg_abs,
+                  uint32_t* __restrict__ next_keys /* null: do not speculate */, uint32_t* __restrict__ next_count) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP];
     __shared__ __align__(128) float2 s_vel[SPH_CAP];
     __shared__ __align__(128) float s_rho[SPH_CAP];
@@ -873,64 +888,78 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     } else {
         force_walk_global<DEBUG, EXACT>(p, pred_s, vel_s, rho, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
     }
-    if (!valid) return;
-
-    // compute.wgsl:90-96
-    const float fvx = fmul(acc.vx, p.visc_coef), fvy = fmul(acc.vy, p.visc_coef);
-    const float ax = fadd(acc.px, fvx), ay = fadd(acc.py, fvy);
-    if (DEBUG) {
-        dbg_accel[out_i] = make_float2(ax, ay);
-        dbg_abs[out_i] = make_float2(acc.ax, acc.ay);
-    }
-    float vx = fadd(vel.x, fmul(fdiv(ax, dens), p.dt));
-    float vy = fadd(vel.y, fmul(fdiv(ay, dens), p.dt));
-    vx = fadd(vx, p.gravity_dt_x);
-    vy = fadd(vy, p.gravity_dt_y);
-    // compute.wgsl:99-108 mouse force
-    if (p.mouse_state != 0) {
-        const float dx = fsub(p.mouse_x, pred.x), dy = fsub(p.mouse_y, pred.y);
-        const float dist = fsqrt(fadd(fmul(dx, dx), fmul(dy, dy)));
-        if (dist <= p.mouse_radius) {
-            const float dirx = fdiv(fdiv(dx, dist), dist), diry = fdiv(fdiv(dy, dist), dist);
-            const float ratio = fdiv(dist, p.mouse_radius);
-            vx = fadd(vx, fmul(fmul(fmul(dirx, p.mouse_power), p.mouse_state_f), ratio));
-            vy = fadd(vy, fmul(fmul(fmul(diry, p.mouse_power), p.mouse_state_f), ratio));
+    float nx = 0.0f, ny = 0.0f, vx = 0.0f, vy = 0.0f;
+    if (valid) {
+        // compute.wgsl:90-96
+        const float fvx = fmul(acc.vx, p.visc_coef), fvy = fmul(acc.vy, p.visc_coef);
+        const float ax = fadd(acc.px, fvx), ay = fadd(acc.py, fvy);
+        if (DEBUG) {
+            dbg_accel[out_i] = make_float2(ax, ay);
+            dbg_abs[out_i] = make_float2(acc.ax, acc.ay);
         }
-    }
-    // compute.wgsl:113-116 NaN guard
-    if (!(vx == vx && vy == vy)) { vx = 0.0f; vy = 0.0f; }
-    // compute.wgsl:118-122 speed clamp
-    const float speed = fsqrt(fadd(fmul(vx, vx), fmul(vy, vy)));
-    if (speed > 500.0f) {
-        vx = fmul(fdiv(vx, speed), 500.0f);
-        vy = fmul(fdiv(vy, speed), 500.0f);
-    }
-    float nx = fadd(pos.x, fmul(vx, p.dt));
-    float ny = fadd(pos.y, fmul(vy, p.dt));
-    // compute.wgsl:127-140 force-field push-out (texel looked up at the PREDICTED position)
-    {
-        const float uvx = fadd(fmul(fdiv(pred.x, p.bounds_x), 1.0f), 0.5f);
-        const float uvy = fadd(fmul(fdiv(pred.y, p.bounds_y), 1.0f), 0.5f);
-        const uint32_t tx = f2u(fmul(uvx, p.tex_w)), ty = f2u(fmul(uvy, p.tex_h));
-        uint32_t tidx = ty * p.tex_wu + tx;
-        if (tidx >= p.tex_len) tidx = p.tex_len - 1u;  // [survey-pinned] out-of-range texel -> last texel
-        const float2 f = __ldg(force_field + tidx);
-        if (f.x != 0.0f || f.y != 0.0f) {
-            const float fwx = fmul(f.x, p.p2w_x), fwy = fmul(f.y, p.p2w_y);
-            const float len = fsqrt(fadd(fmul(f.x, f.x), fmul(f.y, f.y)));
-            const float nnx = fdiv(f.x, len), nny = fdiv(f.y, len);
-            nx = fadd(nx, fwx);
-            ny = fadd(ny, fwy);
-            const float vn = fadd(fmul(vx, nnx), fmul(vy, nny));
-            vx = fsub(vx, fmul(fmul(p.one_minus_damping, vn), nnx));
-            vy = fsub(vy, fmul(fmul(p.one_minus_damping, vn), nny));
+        vx = fadd(vel.x, fmul(fdiv(ax, dens), p.dt));
+        vy = fadd(vel.y, fmul(fdiv(ay, dens), p.dt));
+        vx = fadd(vx, p.gravity_dt_x);
+        vy = fadd(vy, p.gravity_dt_y);
+        // compute.wgsl:99-108 mouse force
+        if (p.mouse_state != 0) {
+            const float dx = fsub(p.mouse_x, pred.x), dy = fsub(p.mouse_y, pred.y);
+            const float dist = fsqrt(fadd(fmul(dx, dx), fmul(dy, dy)));
+            if (dist <= p.mouse_radius) {
+                const float dirx = fdiv(fdiv(dx, dist), dist), diry = fdiv(fdiv(dy, dist), dist);
+                const float ratio = fdiv(dist, p.mouse_radius);
+                vx = fadd(vx, fmul(fmul(fmul(dirx, p.mouse_power), p.mouse_state_f), ratio));
+                vy = fadd(vy, fmul(fmul(fmul(diry, p.mouse_power), p.mouse_state_f), ratio));
+            }
         }
+        // compute.wgsl:113-116 NaN guard
+        if (!(vx == vx && vy == vy)) { vx = 0.0f; vy = 0.0f; }
+        // compute.wgsl:118-122 speed clamp
+        const float speed = fsqrt(fadd(fmul(vx, vx), fmul(vy, vy)));
+        if (speed > 500.0f) {
+            vx = fmul(fdiv(vx, speed), 500.0f);
+            vy = fmul(fdiv(vy, speed), 500.0f);
+        }
+        nx = fadd(pos.x, fmul(vx, p.dt));
+        ny = fadd(pos.y, fmul(vy, p.dt));
+        // compute.wgsl:127-140 force-field push-out (texel looked up at the PREDICTED position)
+        {
+            const float uvx = fadd(fmul(fdiv(pred.x, p.bounds_x), 1.0f), 0.5f);
+            const float uvy = fadd(fmul(fdiv(pred.y, p.bounds_y), 1.0f), 0.5f);
+            const uint32_t tx = f2u(fmul(uvx, p.tex_w)), ty = f2u(fmul(uvy, p.tex_h));
+            uint32_t tidx = ty * p.tex_wu + tx;
+            if (tidx >= p.tex_len) tidx = p.tex_len - 1u;  // [survey-pinned] out-of-range texel -> last texel
+            const float2 f = __ldg(force_field + tidx);
+            if (f.x != 0.0f || f.y != 0.0f) {
+                const float fwx = fmul(f.x, p.p2w_x), fwy = fmul(f.y, p.p2w_y);
+                const float len = fsqrt(fadd(fmul(f.x, f.x), fmul(f.y, f.y)));
+                const float nnx = fdiv(f.x, len), nny = fdiv(f.y, len);
+                nx = fadd(nx, fwx);
+                ny = fadd(ny, fwy);
+                const float vn = fadd(fmul(vx, nnx), fmul(vy, nny));
+                vx = fsub(vx, fmul(fmul(p.one_minus_damping, vn), nnx));
+                vy = fsub(vy, fmul(fmul(p.one_minus_damping, vn), nny));
+            }
+        }
+        // compute.wgsl:143-153 walls
+        if (fabsf(nx) > p.half_x) { nx = fmul(p.half_x, fsign(nx)); vx = fmul(vx, p.neg_damping); }
+        if (fabsf(ny) > p.half_y) { ny = fmul(p.half_y, fsign(ny)); vy = fmul(vy, p.neg_damping); }
+        pos_out[out_i] = make_float2(nx, ny);
+        vel_out[out_i] = make_float2(vx, vy);
     }
-    // compute.wgsl:143-153 walls
-    if (fabsf(nx) > p.half_x) { nx = fmul(p.half_x, fsign(nx)); vx = fmul(vx, p.neg_damping); }
-    if (fabsf(ny) > p.half_y) { ny = fmul(p.half_y, fsign(ny)); vy = fmul(vy, p.neg_damping); }
-    pos_out[out_i] = make_float2(nx, ny);
-    vel_out[out_i] = make_float2(vx, vy);
+    // Speculation for the next tick (single GPU, counting path): with the same delta its K1+K2 (compute.wgsl:8-42) see
+    // exactly this position and velocity, so the key and the per-cell count are emitted here — same functions, same
+    // bits as k_predict_key_count — and the next tick starts at the cell scan. The host drops the speculation when the
+    // next tick's delta differs or the state was replaced (fluid_sim.cu enqueue_tick).
+    if (next_keys) {
+        uint32_t k = 0;
+        if (valid) {
+            const float2 q = predict_position(p, make_float2(nx, ny), make_float2(vx, vy));
+            k = p.key_fast_div ? cell_key_shared(p, q, rcp_refined(p.h)) : cell_key(p, q);
+            next_keys[out_i] = k;
+        }
+        atomic_count_run(next_count, min(k, p.num_cells - 1u), valid);
+    }
 }
 
 }  // namespace fluid

@@ -46,6 +46,12 @@ struct Sim {
     uint32_t* cell_count_buf[2] = {nullptr, nullptr};  // alternate per counted tick; the scan clears the other one
     int cell_count_cur = 0;
     uint32_t* cell_cursor = nullptr;             // small grids (k_cell_scan_small): the cursors live apart from the counts
+    // speculation by the force pass (kernels_sph.cuh): keys (in keys_c) and per-cell counts (in the next count array)
+    // of the NEXT tick, valid if that tick uses the same delta and the state has not been replaced in between
+    bool spec_valid = false;    // the last enqueued tick's force pass speculated and nothing invalidated it since
+    bool count_dirty = false;   // the next count array holds speculative counts (must be cleared if they are not used)
+    float spec_delta = 0.0f;
+    bool speculate = true;      // FLUID_NO_SPECULATION=1: off
     bool pdl = true;                             // programmatic dependent launch on the tick's kernels (FLUID_NO_PDL=1: off)
     uint32_t *cell_tile_sum = nullptr, *cell_tile_max = nullptr;
     float* cell_tile_sq = nullptr;

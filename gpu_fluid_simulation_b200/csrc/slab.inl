@@ -196,7 +196,7 @@ int fluid_slab_sort(FluidSim* h, uint32_t n_from_below, uint32_t n_from_above, u
             memcpy(&sum_sq, &sq_bits, 4);
             counting = s->cell_max_host[0] <= max_ok && sum_sq <= COUNT_SORT_MAX_MEAN_SQ * (float)total;
         }
-        k_cell_reduce<<<s->slab_bin_tiles, CELL_SCAN_THREADS, 0, s->stream>>>(count, s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq);
+        k_cell_reduce<<<s->slab_bin_tiles, CELL_SCAN_THREADS, 0, s->stream>>>(count, s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq, s->d_frame_time, 0u);
         k_cell_downsweep<<<s->slab_bin_tiles, CELL_SCAN_THREADS, 0, s->stream>>>(count, s->slab_bin_lb, s->cell_tile_sum, s->cell_tile_max,
                                                                                s->cell_tile_sq, s->slab_bin_tiles, s->cell_max_dev,
                                                                                s->cell_count_buf[1]);

@@ -109,3 +109,46 @@ def test_auto_switches_when_cells_get_crowded_and_back(fluid, oracle):
         assert np.array_equal(got["grid"], np.sort(keys))
         assert np.array_equal(sim.download_permutation(), np.argsort(keys, kind="stable"))
         assert sim.tick_count == 2 and sim.uniform().frame_time == 2
+
+
+def test_speculated_keys_survive_changes_between_ticks(fluid, oracle):
+    """the force pass emits the next tick's keys and cell counts assuming an unchanged delta and an untouched state; a
+    tick with another delta, an upload, a hash-sort-only tick or a mode switch in between must drop them. Every step is
+    checked against the oracle (bit-exact) and against the radix path, which never speculates."""
+    s, ts, p = scenes.dam_break(48, 160)
+    import dataclasses
+    deltas = [ts.delta, ts.delta, ts.delta * 0.5, ts.delta * 0.5, ts.delta, ts.delta * 2.0, ts.delta, ts.delta]
+    osim = oracle.OracleSim(s, p)
+    sims = {m: fluid.FluidSimulation.new(0, s) for m in (AUTO, RADIX)}
+    try:
+        for m, sim in sims.items():
+            sim.sort_mode = m
+            sim.upload_particles(p)
+        for k, d in enumerate(deltas):
+            tk = dataclasses.replace(ts, delta=d) if dataclasses.is_dataclass(ts) else type(ts)(**{**ts.__dict__, "delta": d})
+            if k == 5:  # replace the state between two ticks: the same particles, shuffled
+                state = sims[RADIX].download_particles()
+                perm = np.random.default_rng(9).permutation(state.shape[0])
+                table = sims[RADIX].download_start_indices()
+                osim.p = state[perm].copy()
+                for sim in sims.values():
+                    sim.upload_particles(state[perm])
+                    sim.upload_start_indices(table)
+            osim.tick(tk)
+            outs = {}
+            for m, sim in sims.items():
+                sim.tick(tk)
+                outs[m] = (sim.download_particles(), sim.download_start_indices(), sim.download_unsorted_keys())
+            for a, b in zip(outs[AUTO], outs[RADIX]):
+                assert np.array_equal(a, b), k
+            got = outs[AUTO][0]
+            assert np.array_equal(outs[AUTO][1], osim.table), k
+            for f in ("grid", "position", "predicted_position", "velocity", "density"):
+                assert np.array_equal(got[f], osim.p[f]), (k, f)
+            if k == 3:  # a hash-sort-only tick in between (reorders the state, runs no force pass)
+                for sim in sims.values():
+                    sim.tick_hash_sort_only(tk)
+                osim.tick(tk, stop_after=1)
+    finally:
+        for sim in sims.values():
+            sim.close()
