@@ -105,6 +105,7 @@ PROTOTYPES = {
     "fluid_sim_download_debug_force": (_i, [_P, _P, _P]),
     "fluid_sim_download_permutation": (_i, [_P, _P]),
     "fluid_sim_device_view": (_i, [_P, C.POINTER(DeviceView)]),
+    "fluid_sim_state_changed": (_i, [_P]),
     "fluid_sim_stream": (_P, [_P]),
     "fluid_sim_enable_timing": (_i, [_P, _i]),
     "fluid_sim_last_timing": (_i, [_P, C.POINTER(C.c_char_p), C.POINTER(C.c_float), _i]),

@@ -751,6 +751,12 @@ int fluid_sim_device_view(FluidSim* h, FluidSimDeviceView* out) {
     out->start_indices = s->start_indices; out->cell_lower_bound = s->cell_lb; out->force_field = s->force_field;
     return FLUID_OK;
 }
+int fluid_sim_state_changed(FluidSim* h) {
+    SIM_OR_FAIL(h);
+    s->spec_valid = false;
+    s->cell_max_known = false;
+    return FLUID_OK;
+}
 void* fluid_sim_stream(FluidSim* h) { return h ? (void*)reinterpret_cast<Sim*>(h)->stream : nullptr; }
 
 int fluid_sim_enable_timing(FluidSim* h, int enable) {

@@ -208,6 +208,10 @@ class FluidSimulation:
     def download_particles_async(self, out):
         _lib.check(self._lib.fluid_sim_download_particles_async(self._h, _lib.ptr(out)))
 
+    def state_changed(self):
+        """call after writing position / velocity through the device pointers of device_view()"""
+        _lib.check(self._lib.fluid_sim_state_changed(self._h))
+
     def sync_transfers(self):
         _lib.check(self._lib.fluid_sim_sync_transfers(self._h))
 

@@ -221,6 +221,10 @@ typedef struct FluidSimDeviceView {
     void* force_field;        /* float2[tex_w*tex_h] */
 } FluidSimDeviceView;
 int fluid_sim_device_view(FluidSim* sim, FluidSimDeviceView* out);
+/* A consumer that WRITES position or velocity through the pointers above (instead of fluid_sim_upload_particles) must
+ * say so before the next tick: the library carries work from one tick into the next (the force pass emits the next
+ * tick's keys and cell counts, the sort path is chosen from the previous ticks' cell statistics). */
+int fluid_sim_state_changed(FluidSim* sim);
 void* fluid_sim_stream(FluidSim* sim); /* cudaStream_t */
 
 /* per-phase device timing (CUDA events on the handle's stream), averaged over the ticks

@@ -53,6 +53,7 @@ extern "C" {
     fn fluid_sim_upload_particles_async(sim: *mut FluidSim, src: *const ParticleInstance) -> c_int;
     fn fluid_sim_download_particles_async(sim: *mut FluidSim, dst: *mut ParticleInstance) -> c_int;
     fn fluid_sim_sync_transfers(sim: *mut FluidSim) -> c_int;
+    fn fluid_sim_state_changed(sim: *mut FluidSim) -> c_int;
 }
 
 fn check(rc: c_int) {
@@ -138,6 +139,8 @@ impl FluidSimulation {
         assert_eq!(dst.len(), self.settings.particle_count as usize);
         check(fluid_sim_download_particles_async(self.handle, dst.as_mut_ptr()));
     }
+    /// after writing position / velocity through raw device pointers (zero-copy consumers)
+    pub fn state_changed(&mut self) { check(unsafe { fluid_sim_state_changed(self.handle) }); }
     pub fn sync_transfers(&mut self) { check(unsafe { fluid_sim_sync_transfers(self.handle) }); }
     pub fn restart(&mut self, device_ordinal: i32) { *self = Self::new(device_ordinal, self.settings); }
     pub fn cuda_stream(&mut self) -> *mut c_void { unsafe { fluid_sim_stream(self.handle) } }
