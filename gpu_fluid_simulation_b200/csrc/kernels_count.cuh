@@ -7,11 +7,16 @@
 // A key IS a cell id (funcs.wgsl:216-218), there are ~4 particles per cell and `cell_lb` — the exclusive prefix sum of
 // the per-cell particle counts — has to be built anyway. So instead of three 8-bit radix passes over (key, index):
 //   1. k_predict_key_count   predict + key (K1+K2, compute.wgsl:8-42) and count[key] += 1           (one RED per run)
-//   2. k_cell_reduce / k_cell_downsweep   cell_lb = exclusive scan of count; cursor = cell_lb; largest count -> host
+//                            — in steady state not launched at all: the previous tick's force pass has emitted the
+//                            keys and the counts (kernels_sph.cuh, "speculation"; fluid_sim.cu enqueue_tick decides)
+//   2. k_cell_reduce / k_cell_downsweep   cell_lb = exclusive scan of count; cursor = cell_lb; cell statistics -> host;
+//                            clears the count array of the next tick. Grids of <= 32 tiles: k_cell_scan_small, one launch
 //   3. k_cell_slots          slot = cursor[key]++ : writes (key, source index) into the cell's block, in ARRIVAL order
 //   4. k_rank_gather_cells   puts each cell's block into source-index order (rank = entries of the cell with a
 //                            smaller index), which makes the result the STABLE sort — exactly the order the LSD radix
-//                            passes produce, so the float sums downstream do not change a bit — and moves the payload.
+//                            passes produce, so the float sums downstream do not change a bit — moves the payload and
+//                            makes the staging plans of the neighbour passes.
+// Slab mode (slab.inl) runs the same steps over a band's cells: k_count_keys, the scan, k_cell_slots, k_slab_rank_gather.
 // Traffic per particle: 20 + 12 + ~56 B against 20 + 44 + 60 B for hash + 3 onesweep passes + gather.
 // The atomics are cheap because the array enters a tick in the previous tick's key order: along the lanes of a warp
 // the keys come in runs, the head of a run issues one atomic for the whole run, and the lanes of one instruction

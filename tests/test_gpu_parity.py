@@ -316,7 +316,8 @@ def test_config3_full_step_1m_dambreak(fluid, oracle):
 
 def test_16m_full_step_bit_exact(fluid, oracle):
     """16M particles, two ticks, every field of every particle against the oracle (the 64M scene of bench.py is checked
-    the same way by scripts/verify_full_size.py; result of the last run: profiles/r1c_verify_64m.json)."""
+    the same way by scripts/verify_full_size.py; results: profiles/r1d_verify_64m.json on the counting path,
+    profiles/r1c_verify_64m.json on the radix path)."""
     s, ts, p = scenes.uniform_box(4000)
     osim = oracle.OracleSim(s, p, sort_mode=oracle.SORT_COUNTING)  # stable counting sort == the stable radix order
     with fluid.FluidSimulation.new(0, s) as sim:
