@@ -8,7 +8,8 @@
 A "step" is one complete tick (predict, hash, sort, cell tables, density, force+integrate) of the workload.
 Default workload: the 64M-particle uniform box of BASELINE.json config 5 (the size the metric's target is quoted
 on; ~4 GB of particle state, far larger than the 126 MB L2, so no L2 flush is needed between steps). At N > 1 the
-same 64M box is partitioned into y-slabs over the ranks (strong scaling), with NCCL halo exchange and migration.
+same 64M box is cut into bands of grid rows over the ranks (strong scaling); the step and its one NCCL exchange per tick run
+inside the library (fluid_multi_tick), and the run first checks the NCCL path bit for bit against one GPU.
 
 One JSON line is printed by rank 0. `value` is device-timed (CUDA events on the library's stream, inputs resident
 in HBM); `e2e` is measured through the public API with HOST buffers (pinned upload of the full particle state +
@@ -106,50 +107,75 @@ def make_scene(name):
     return SimulationSettings(), TickSettings(), None  # default lattice is built by create()
 
 
-def cpu_sample_scene(workload):
-    """bounded sample of the workload for the CPU arm: same spacing / h / parameters, 1M (or 256K) particles."""
+def cpu_sample_scene(workload, full=False):
+    """the CPU arm's scene: the named workload itself (full=True) or a bounded sample of it — same spacing / h / tick
+    parameters, 1M particles."""
     from gpu_fluid_simulation_b200 import scenes
-    kind, _ = WORKLOADS[workload]
+    kind, arg = WORKLOADS[workload]
+    if full:
+        return make_scene(workload), f"the {workload} workload itself"
     if kind == "dam":
         return scenes.dam_break(500, 2000), "1M-particle dam-break (same spacing, h and tick parameters)"
+    if kind == "default":
+        return make_scene(workload), "the reference's default scene (100,000 particles) itself"
     return scenes.uniform_box(1000), "1M-particle sub-box of the uniform box (same spacing, h, jitter and tick parameters)"
 
 
-def run_cpu(workload, ticks, warmup=1, budget_s=25.0):
-    """times the CPU oracle (port of the reference's WGSL step; counting sort = the fair CPU variant)."""
+def host_cores():
+    """the cores this process may run on (torchrun exports OMP_NUM_THREADS=1 to its workers: the CPU arm must not inherit
+    that, it is the reference's all-core CPU figure)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_cpu(workload, ticks, warmup=1, budget_s=25.0, full=False):
+    """times the CPU oracle (port of the reference's WGSL step; counting sort = the fair CPU variant) on every host core."""
     from oracle import oracle as O
     O.build()
-    (s, ts, p), desc = cpu_sample_scene(workload)
+    O.lib().oracle_set_num_threads(host_cores())
+    (s, ts, p), desc = cpu_sample_scene(workload, full)
     sim = O.OracleSim(s, p, sort_mode=O.SORT_COUNTING)
+    t_w = time.perf_counter()
+    warm_done = 0
     for _ in range(warmup):
         sim.tick(ts)
+        warm_done += 1
+        if budget_s and time.perf_counter() - t_w > 0.4 * budget_s:
+            break
     t0 = time.perf_counter()
     done = 0
-    per = []
     while done < ticks:
-        t1 = time.perf_counter()
         sim.tick(ts)
-        per.append(time.perf_counter() - t1)
         done += 1
         if budget_s and time.perf_counter() - t0 > budget_s:
             break
     dt = time.perf_counter() - t0
     n = s.particle_count
     return {"value": n * done / dt, "unit": "particle-steps/s", "cores": int(O.lib().oracle_num_threads()), "kind": "port",
-            "sample": f"{done} ticks of a {desc}; OpenMP over particles, stable counting sort", "ms_per_step": 1e3 * dt / done,
-            "particles": n, "ticks": done}
+            "sample": f"{done} ticks (after {warm_done} warm-up) of {desc}; OpenMP over particles on {int(O.lib().oracle_num_threads())} "
+                      "threads, stable counting sort", "ms_per_step": 1e3 * dt / done,
+            "particles": n, "ticks": done, "warmup": warm_done}
 
 
 def reference_arm(args, rank):
+    """--impl reference: the reference's step on the host cores. The reference has no CPU implementation of this path
+    and its WGSL cannot run here, so this is the oracle port (kind "port"), on the NAMED workload when a tick of it is
+    affordable (64M: ~5 s per tick on 32 cores), else on the 1M-particle sample (config.particles says which)."""
     if rank != 0:
         return
-    t_budget = 150.0
-    r = run_cpu(args.workload, args.steps, warmup=max(1, min(args.warmup, 2)), budget_s=t_budget)
+    n_named = {"uniform": lambda a: a * a, "dam": lambda a: a[0] * a[1], "default": lambda a: 100_000}[WORKLOADS[args.workload][0]](WORKLOADS[args.workload][1])
+    full = os.environ.get("FLUID_REF_SAMPLE", "") != "1" and (n_named <= 4_000_000 or (host_cores() >= 8 and args.steps <= 64))
+    steps = args.steps
+    r = run_cpu(args.workload, steps, warmup=args.warmup, budget_s=150.0, full=full)
     line = {"impl": "reference", "metric": "particle-steps/sec", "value": r["value"], "unit": "particle-steps/s",
-            "n_gpus": args.gpus, "steps": r["ticks"], "warmup": max(1, min(args.warmup, 2)), "ms_per_step": r["ms_per_step"],
+            "n_gpus": args.gpus, "steps": r["ticks"], "warmup": r["warmup"], "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": args.workload, "note": "CPU oracle (C++ restatement of the reference's WGSL step; the "
-                       "reference's own wgpu/WGSL path is unavailable on this box) on a bounded sample of the workload"},
+            "config": {"workload": args.workload, "particles": r["particles"], "same_config": bool(full),
+                       "note": "CPU oracle (C++ restatement of the reference's WGSL step; the reference's own wgpu/WGSL path is "
+                               "unavailable on this box); every step is one full tick" + ("" if full else " of a bounded 1M-particle sample of the workload")
+                               + "; steps / warm-up are cut short when the time budget (150 s + 60 s) runs out"},
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": "particle-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -170,6 +196,7 @@ def main():
                     help="key-order path of the single-GPU tick (include/fluid_b200.h FLUID_SORT_*): identical results")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="--gpus > 1: skip the NCCL-path-vs-single-GPU parity check before timing")
     ap.add_argument("--e2e-steps", type=int, default=6)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -192,8 +219,8 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the fluid step has no CPU fallback")
     torch.cuda.set_device(local_rank)
     if world > 1:
-        from gpu_fluid_simulation_b200.slab import run_slab_bench
-        line = run_slab_bench(args, rank, world, local_rank, WORKLOADS, ALGO_BYTES, *peaks(), ClockSampler)
+        from gpu_fluid_simulation_b200.multi_bench import run_multi_bench
+        line = run_multi_bench(args, rank, world, local_rank, WORKLOADS, ALGO_BYTES, *peaks(), ClockSampler)
         if rank == 0:
             print(json.dumps(line), flush=True)
         return

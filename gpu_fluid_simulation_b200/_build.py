@@ -7,13 +7,13 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "libfluid_b200.so")
 SOURCES = ["fluid_sim.cu", "jfa.cu", "selftest.cu", "render.cu", "dormant.cu"]
-HEADERS = ["slab.inl", "field.inl", "kernels_slab.cuh", "slab_rows.h", "common.cuh", "radix_sort.cuh", "kernels_hash.cuh", "kernels_cells.cuh", "kernels_count.cuh", "kernels_sph.cuh", "sim_internal.h",
+HEADERS = ["multi.inl", "field.inl", "kernels_band.cuh", "common.cuh", "radix_sort.cuh", "kernels_hash.cuh", "kernels_cells.cuh", "kernels_count.cuh", "kernels_sph.cuh", "sim_internal.h",
            os.path.join("..", "..", "include", "fluid_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC,-ffp-contract=off,-fno-fast-math", "--fmad=true",  # exact paths use __f*_rn intrinsics explicitly
-    "-shared",
+    "-shared", "-ldl",
 ]
 
 

@@ -57,12 +57,10 @@ class DeviceView(C.Structure):
                 ("force_field", C.c_void_p)]
 
 
-class SlabView(C.Structure):
-    _fields_ = [("n", C.c_uint32), ("pad", C.c_uint32), ("capacity", C.c_uint32), ("emig_cap", C.c_uint32),
-                ("pos_state", C.c_void_p), ("vel_state", C.c_void_p), ("pos_sorted", C.c_void_p),
-                ("pred_sorted", C.c_void_p), ("vel_sorted", C.c_void_p), ("rho", C.c_void_p), ("keys_ext", C.c_void_p),
-                ("emig_list", C.c_void_p), ("emig_count", C.c_void_p), ("meta", C.c_void_p), ("start_indices", C.c_void_p),
-                ("dyn", C.c_void_p)]
+class MultiOptions(C.Structure):
+    """FluidMultiOptions (include/fluid_b200.h)."""
+    _fields_ = [("row_bounds", C.c_uint32 * 9), ("capacity", C.c_uint32), ("window_near", C.c_uint32),
+                ("window_far", C.c_uint32), ("transport", C.c_int32), ("reserved", C.c_uint32 * 4)]
 
 
 _P = C.c_void_p
@@ -112,15 +110,34 @@ PROTOTYPES = {
     "fluid_sim_launch_count": (C.c_uint64, [_P]),
     "fluid_sim_reserve": (_i, [_P, _u32]),
     "fluid_sim_set_particle_count": (_i, [_P, _u32]),
-    "fluid_slab_configure": (_i, [_P, _i, _i, _P, _u32, _u32, _u32]),
-    "fluid_slab_view": (_i, [_P, C.POINTER(SlabView)]),
-    "fluid_slab_begin_tick": (_i, [_P, C.POINTER(TickSettingsC)]),
-    "fluid_slab_pack": (_i, [_P, _u32, _P]),
-    "fluid_slab_unpack": (_i, [_P, _P, _u32, _u32]),
-    "fluid_slab_sort": (_i, [_P, _u32, _u32, _u32]),
-    "fluid_slab_cells_density": (_i, [_P, _u32, _u32, _u32, _u32, _u32]),
-    "fluid_slab_cells_density_dev": (_i, [_P, _P]),
-    "fluid_slab_force": (_i, [_P]),
+    "fluid_multi_create": (_i, [C.POINTER(SimSettings), _i, C.POINTER(_i), C.POINTER(MultiOptions), C.POINTER(_P)]),
+    "fluid_multi_unique_id": (_i, [_P]),
+    "fluid_multi_create_rank": (_i, [C.POINTER(SimSettings), _i, _i, _P, _i, C.POINTER(MultiOptions), C.POINTER(_P)]),
+    "fluid_multi_destroy": (None, [_P]),
+    "fluid_multi_tick": (_i, [_P, C.POINTER(TickSettingsC)]),
+    "fluid_multi_tick_n": (_i, [_P, C.POINTER(TickSettingsC), _u32]),
+    "fluid_multi_sync": (_i, [_P]),
+    "fluid_multi_tick_count": (_u32, [_P]),
+    "fluid_multi_set_tick_count": (_i, [_P, _u32]),
+    "fluid_multi_set_math_mode": (_i, [_P, _i]),
+    "fluid_multi_world": (_i, [_P]),
+    "fluid_multi_local_bands": (_i, [_P]),
+    "fluid_multi_transport": (_i, [_P]),
+    "fluid_multi_row_bounds": (_i, [_P, _P]),
+    "fluid_multi_upload_particles": (_i, [_P, _P, _u32]),
+    "fluid_multi_download_particles": (_i, [_P, _P]),
+    "fluid_multi_upload_band": (_i, [_P, _P, _u32, _P]),
+    "fluid_multi_download_band": (_i, [_P, _i, _P, _u32, C.POINTER(_u32), C.POINTER(_u32)]),
+    "fluid_multi_particle_counts": (_i, [_P, _P]),
+    "fluid_multi_download_start_indices": (_i, [_P, _P]),
+    "fluid_multi_upload_start_indices": (_i, [_P, _P]),
+    "fluid_multi_upload_force_field": (_i, [_P, _P]),
+    "fluid_multi_enable_timing": (_i, [_P, _i]),
+    "fluid_multi_last_timing": (_i, [_P, _i, C.POINTER(C.c_char_p), C.POINTER(C.c_float), _i]),
+    "fluid_multi_launch_count": (C.c_uint64, [_P]),
+    "fluid_multi_stream": (_P, [_P, _i]),
+    "fluid_multi_band_sim": (_P, [_P, _i]),
+    "fluid_multi_balanced_bounds": (_i, [C.POINTER(SimSettings), _P, _u32, _i, _P]),
     "fluid_jfa_run": (_i, [_P, _u32, _u32, _P, _i]),
     "fluid_jfa_pass": (_i, [_P, _u32, _u32, _u32, _P, _i]),
     "fluid_jfa_seed_from_mask": (_i, [_P, _u32, _u32, _P, _i]),

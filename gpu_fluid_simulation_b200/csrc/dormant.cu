@@ -98,7 +98,7 @@ using namespace fluid;
 extern "C" int fluid_sim_surface_tension(FluidSim* h_, float* force_xy_out) {
     if (!h_ || !force_xy_out) { set_error("fluid_sim_surface_tension: null argument"); return FLUID_ERR_INVALID_ARGUMENT; }
     Sim* s = reinterpret_cast<Sim*>(h_);
-    if (s->slab) { set_error("fluid_sim_surface_tension: not available on a slab handle"); return FLUID_ERR_UNSUPPORTED; }
+    if (s->band) { set_error("fluid_sim_surface_tension: not available on a band of a FluidMulti"); return FLUID_ERR_UNSUPPORTED; }
     FLUID_CUDA(cudaSetDevice(s->device));
     if (s->n == 0) return FLUID_OK;
     const FluidSimUniform& u = s->last_uniform;

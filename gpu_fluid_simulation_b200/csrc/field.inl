@@ -9,7 +9,7 @@
 // converted in place into the sim's force-field buffer: same frame, no host round trip.
 //
 // Pinned arithmetic of the mask (WGSL leaves interpolation, sin/cos and distance accuracy to the implementation;
-// the CPU restatement oracle_rasterize_objects pins the same choices): pixel-centre clip coordinates
+// the CPU restatement used by the tests pins the same choices): pixel-centre clip coordinates
 // cx = ((px+0.5)/w - 0.5)*2, cy = -(((py+0.5)/h - 0.5)*2) (framebuffer row 0 is clip y = +1); inv_pos rows
 // evaluated as (m0r*cx + m1r*cy) + m3r (z = 0 contributes exactly nothing, w = 1); IEEE binary32 without
 // contraction, correctly rounded / and sqrt; cos(-rot), sin(-rot) evaluated once per object on the host (libm).

@@ -220,14 +220,15 @@ void launch_tile_plans(Sim* s, const DevParams& p, const uint32_t* keys, bool pd
 }
 
 void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, float2* vel_out, bool pdl = false,
-                  uint32_t* next_keys = nullptr, uint32_t* next_count = nullptr) {
+                  uint32_t* next_keys = nullptr, uint32_t* next_count = nullptr, const uint32_t* band_range = nullptr,
+                  const uint32_t* goff_dev = nullptr) {
     float2* da = s->debug_force ? s->dbg_accel : nullptr;
     float2* db = s->debug_force ? s->dbg_abs : nullptr;
-    const uint32_t* keys = s->slab ? s->keys_ext : s->keys_sorted;
+    const uint32_t* keys = s->keys_sorted;
 #define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                     \
     launch_pdl(pdl, k_force_integrate<DBG, EX>, dim3(blocks), dim3(SPH_THREADS), s->stream, p, s->pos_s, s->pred_s, s->vel_s, \
-               s->rho, keys, s->cell_lb, s->quirk, s->force_field, s->d_frame_time, s->slab_goff_dev, s->quirk + 2,     \
-               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db, next_keys, next_count)
+               s->rho, keys, s->lb_view, s->quirk, s->force_field, s->d_frame_time, goff_dev, s->quirk + 2,             \
+               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db, next_keys, next_count, band_range)
     if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
     else { if (s->exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
 #undef FLUID_LAUNCH_FORCE
@@ -310,7 +311,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     }
     if (counting) {
         launch_pdl(pdl, k_cell_slots, dim3((n + GATHER_THREADS * SLOT_ITEMS - 1) / (GATHER_THREADS * SLOT_ITEMS)), dim3(GATHER_THREADS),
-                   stream, n, 0u, p.num_cells - 1u, keys_u, cursor, keys_b, idx_a);
+                   stream, n, 0u, p.num_cells - 1u, keys_u, cursor, keys_b, idx_a, (const uint32_t*)nullptr);
         launches++;
         mark("sort");
         launch_pdl(pdl, k_rank_gather_cells, dim3((n + GATHER_THREADS * RANK_ITEMS - 1) / (GATHER_THREADS * RANK_ITEMS)),
@@ -380,7 +381,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     const uint32_t sblocks = (n + SPH_THREADS - 1) / SPH_THREADS;
     if (!counting) launch_tile_plans(this, p, keys_sorted, pdl);  // counting path: made by k_rank_gather_cells
     launch_pdl(pdl, k_density, dim3(sblocks), dim3(SPH_THREADS), stream, p, pred_s, keys_sorted, cell_lb, quirk, rho, quirk + 2,
-               d_frame_time, reinterpret_cast<const TilePlan*>(tile_plans));
+               d_frame_time, reinterpret_cast<const TilePlan*>(tile_plans), (const uint32_t*)nullptr);
     launches++;
     mark("density");
     // the force pass emits the next tick's keys (into keys_c: free on the counting path, and the radix passes of THIS tick are
@@ -409,10 +410,16 @@ int fluid_device_count(void) {
     return c;
 }
 
-int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** out) {
-    if (!s || !out) return invalid("fluid_sim_create: null argument");
+int fluid_sim_upload_particles(FluidSim* h, const FluidParticle* src);
+void fluid_sim_destroy(FluidSim* h);
+
+}  // extern "C"
+
+namespace fluid {
+// the handle behind fluid_sim_create; a band of the multi-GPU step (multi.inl) is the same object with room for
+// `capacity` particles and no initial lattice
+int sim_create_internal(const FluidSimSettings* s, int device_ordinal, uint32_t capacity, bool lattice, Sim** out) {
     *out = nullptr;
-    if (s->particle_count < 2) return invalid("fluid_sim_create: particle_count < 2 (the reference panics: (0).ilog2(), src/simulation.rs:323-324)");
     if (!(s->smoothing_radius > 0.0f) || !(s->size[0] > 0.0f) || !(s->size[1] > 0.0f))
         return invalid("fluid_sim_create: smoothing_radius and size must be positive");
     if (s->texture_size[0] == 0 || s->texture_size[1] == 0) return invalid("fluid_sim_create: texture_size must be non-zero");
@@ -432,7 +439,7 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
     sim->device = device_ordinal;
     sim->num_sms = prop.multiProcessorCount;
     sim->settings = *s;
-    sim->n = s->particle_count;
+    sim->n = lattice ? s->particle_count : 0u;
     // src/simulation.rs:140-141
     sim->grid_w = (uint32_t)(size_t)ceilf(s->size[0] / s->smoothing_radius) + 2u;
     sim->grid_h = (uint32_t)(size_t)ceilf(s->size[1] / s->smoothing_radius) + 2u;
@@ -443,7 +450,7 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
     int rc = FLUID_OK;
     auto fail = [&](int code) { fluid_sim_destroy(reinterpret_cast<FluidSim*>(sim)); return code; };
     if (cudaStreamCreateWithFlags(&sim->stream, cudaStreamNonBlocking) != cudaSuccess) return fail(cuda_fail(cudaGetLastError(), "cudaStreamCreate", __FILE__, __LINE__));
-    if ((rc = sim->alloc(sim->n)) != FLUID_OK) return fail(rc);
+    if ((rc = sim->alloc(capacity)) != FLUID_OK) return fail(rc);
     const size_t tex_len = (size_t)s->texture_size[0] * s->texture_size[1];
     // cell tables padded to whole scan tiles (kernels_count.cuh); the pad of cell_lb includes entry [num_cells]
     sim->cell_tiles = (uint32_t)(((size_t)sim->num_cells + 1 + CELL_SCAN_TILE - 1) / CELL_SCAN_TILE);
@@ -468,6 +475,7 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
     cudaMemsetAsync(sim->cell_count_buf[1], 0, cells_padded * 4, sim->stream);
     sim->cell_max_host[0] = 0;
     sim->cell_max_host[1] = 0;
+    sim->lb_view = sim->cell_lb;
     {
         const char* no_pdl = getenv("FLUID_NO_PDL");
         sim->pdl = !(no_pdl && no_pdl[0] == '1');
@@ -481,7 +489,7 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
     cudaFuncSetAttribute(k_onesweep_pass<SORT_ITEMS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SORT_TILE * 8);
 
     // init lattice, src/simulation.rs:147-163 (host arithmetic, uploaded once like create_buffer_init :168-172)
-    {
+    if (lattice) {
         const uint32_t n = sim->n;
         std::vector<FluidParticle> host(n);
         const float ppr = sqrtf((float)n);
@@ -503,9 +511,24 @@ int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** o
     memset(&zero_tick, 0, sizeof zero_tick);
     sim->make_uniform(zero_tick, 0, &sim->last_uniform);
     if (cudaStreamSynchronize(sim->stream) != cudaSuccess) return fail(cuda_fail(cudaGetLastError(), "sync after create", __FILE__, __LINE__));
+    *out = sim;
+    return FLUID_OK;
+}
+}  // namespace fluid
+
+extern "C" {
+
+int fluid_sim_create(const FluidSimSettings* s, int device_ordinal, FluidSim** out) {
+    if (!s || !out) return invalid("fluid_sim_create: null argument");
+    *out = nullptr;
+    if (s->particle_count < 2) return invalid("fluid_sim_create: particle_count < 2 (the reference panics: (0).ilog2(), src/simulation.rs:323-324)");
+    Sim* sim = nullptr;
+    int rc = sim_create_internal(s, device_ordinal, s->particle_count, true, &sim);
+    if (rc != FLUID_OK) return rc;
     *out = reinterpret_cast<FluidSim*>(sim);
     return FLUID_OK;
 }
+
 
 void fluid_sim_destroy(FluidSim* h) {
     if (!h) return;
@@ -514,8 +537,8 @@ void fluid_sim_destroy(FluidSim* h) {
     if (s->stream) cudaStreamSynchronize(s->stream);
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
                     s->idx_b, s->sort_scratch, s->tile_plans, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
-                    s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b, s->keys_ext, s->emig_list, s->slab_meta,
-                    s->mask_dev, s->mask_flag, s->objects_dev, s->slab_dyn, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq, s->slab_bin_lb, s->cell_cursor};
+                    s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b,
+                    s->mask_dev, s->mask_flag, s->objects_dev, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq, s->cell_cursor};
     for (void* b : bufs) if (b) cudaFree(b);
     if (s->cell_max_host) cudaFreeHost((void*)s->cell_max_host);
     if (s->h2d_stream) { cudaStreamSynchronize(s->h2d_stream); cudaStreamDestroy(s->h2d_stream); }
@@ -534,7 +557,7 @@ void fluid_sim_destroy(FluidSim* h) {
     Sim* s = reinterpret_cast<Sim*>(h);                                  \
     FLUID_CUDA(cudaSetDevice(s->device));
 
-#define NOT_SLAB(s) if ((s)->slab) return invalid("handle is in slab mode: drive it with the fluid_slab_* phases")
+#define NOT_SLAB(s) if ((s)->band) return invalid("handle is a band of a FluidMulti: drive it through fluid_multi_*")
 
 int fluid_sim_tick(FluidSim* h, const FluidTickSettings* t) {
     SIM_OR_FAIL(h);
@@ -716,7 +739,7 @@ int fluid_sim_download_permutation(FluidSim* h, uint32_t* dst) {
     SIM_OR_FAIL(h);
     if (!dst) return invalid("null destination");
     if (!s->idx_sorted) return invalid("fluid_sim_download_permutation: no tick has run yet");
-    if (!s->slab && s->last_sort_path == FLUID_SORT_COUNTING) {
+    if (!s->band && s->last_sort_path == FLUID_SORT_COUNTING) {
         k_rank_permutation<<<(s->n + GATHER_THREADS - 1) / GATHER_THREADS, GATHER_THREADS, 0, s->stream>>>(
             s->n, s->num_cells, s->keys_b, s->idx_a, s->cell_lb, s->idx_b);
         s->launches++;
@@ -785,7 +808,7 @@ int fluid_sim_last_timing(FluidSim* h, const char** names, float* ms, int cap) {
         if (ms) ms[out] = (float)(sum / (double)ticks);
     }
     // device time between the last mark of a tick and the first mark of the next one: zero while the host keeps the
-    // stream fed, the host's lag otherwise (slab mode: everything the driver does between two ticks)
+    // stream fed, the host's lag otherwise
     if (ticks >= 2 && out < cap && s->marks_per_tick >= 2) {
         double sum = 0.0;
         for (uint64_t t = 0; t + 1 < ticks; t++) {
@@ -869,12 +892,7 @@ int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
 }
 int fluid_sim_set_particle_count(FluidSim* h, uint32_t n) {
     SIM_OR_FAIL(h);
-    if (s->slab) {
-        if (n > s->slab_capacity) return invalid("fluid_sim_set_particle_count: n exceeds the slab capacity");
-        s->n = n;
-        s->cell_max_known = false;
-        return FLUID_OK;
-    }
+    NOT_SLAB(s);
     if (n < 2 || n > s->capacity) return invalid("fluid_sim_set_particle_count: need 2 <= n <= capacity");
     s->n = n;
     s->cell_max_known = false;
@@ -884,4 +902,4 @@ int fluid_sim_set_particle_count(FluidSim* h, uint32_t n) {
 
 }  // extern "C"
 
-#include "slab.inl"
+#include "multi.inl"

@@ -16,7 +16,8 @@
 //                            smaller index), which makes the result the STABLE sort — exactly the order the LSD radix
 //                            passes produce, so the float sums downstream do not change a bit — moves the payload and
 //                            makes the staging plans of the neighbour passes.
-// Slab mode (slab.inl) runs the same steps over a band's cells: k_count_keys, the scan, k_cell_slots, k_slab_rank_gather.
+// The multi-GPU step (kernels_band.cuh) runs the same steps over a band's cells: k_band_key / k_band_recv count, the scan,
+// k_cell_slots, k_band_rank_gather (in-cell order by origin instead of by index).
 // Traffic per particle: 20 + 12 + ~56 B against 20 + 44 + 60 B for hash + 3 onesweep passes + gather.
 // The atomics are cheap because the array enters a tick in the previous tick's key order: along the lanes of a warp
 // the keys come in runs, the head of a run issues one atomic for the whole run, and the lanes of one instruction
@@ -287,10 +288,12 @@ k_cell_scan_small(const uint32_t* __restrict__ count, uint32_t* __restrict__ cur
 constexpr int SLOT_ITEMS = FLUID_SLOT_ITEMS;
 __global__ void __launch_bounds__(GATHER_THREADS)
 k_cell_slots(uint32_t n, uint32_t key_lo, uint32_t last_bin, const uint32_t* __restrict__ keys_u, uint32_t* __restrict__ cursor,
-             uint32_t* __restrict__ slot_keys, uint32_t* __restrict__ slot_idx) {
-    // bin of a key = clamp(key - key_lo, 0, last_bin): (0, num_cells - 1) on one GPU; a slab rank passes its band's first
-    // cell and one bin past its last for the sentinel key of emigrants (count_bin)
+             uint32_t* __restrict__ slot_keys, uint32_t* __restrict__ slot_idx, const uint32_t* __restrict__ n_dev) {
+    // bin of a key = clamp(key - key_lo, 0, last_bin): (0, num_cells - 1) on one GPU; a band of the multi-GPU step passes the
+    // first cell of its table and one bin past the last for the sentinel key of departed particles (count_bin), and
+    // the number of entries through `n_dev` (only the device knows it; `n` then bounds the grid)
     pdl_enter();
+    if (n_dev) n = __ldg(n_dev);
     const uint32_t lane = lane_id();
     const uint32_t warp = (blockIdx.x * GATHER_THREADS + threadIdx.x) >> 5;
     const uint32_t first = warp * (32u * SLOT_ITEMS) + lane;
@@ -403,17 +406,6 @@ k_rank_gather_cells(const DevParams p, const uint32_t* __restrict__ slot_keys, c
             }
         }
     }
-}
-
-// slab mode: the keys exist already (k_slab_key_hist makes them while it detects emigrants); count them per bin.
-// The last bin belongs to the sentinel key of emigrants: they are NOT counted, so the scan's statistics cover real cells
-// only and the last bin starts at the owned count; the slot pass still hands them (unused) slots behind it.
-__global__ void __launch_bounds__(GATHER_THREADS)
-k_count_keys(const uint32_t* __restrict__ keys, uint32_t n, uint32_t key_lo, uint32_t last_bin, uint32_t* __restrict__ count) {
-    const uint32_t i = blockIdx.x * GATHER_THREADS + threadIdx.x;  // grid is a whole number of warps
-    const uint32_t k = i < n ? __ldg(keys + i) : 0u;
-    const uint32_t bin = count_bin(k, key_lo, last_bin);
-    cell_count_add(count, bin, i < n && bin != last_bin);
 }
 
 // the source permutation (sorted index -> index before the tick) is a parity tap only: computed on request from the

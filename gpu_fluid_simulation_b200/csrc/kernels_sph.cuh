@@ -71,11 +71,10 @@ struct __align__(16) TilePlan {
 };
 static_assert(sizeof(TilePlan) == 64, "TilePlan is read as four 16-byte words");
 
-__device__ __forceinline__ void make_tile_plan(const DevParams& p, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ lb,
-                                               uint32_t tile, TilePlan* __restrict__ plans) {
+// [i0, i1): the tile's sorted particles (i1 > i0); `plans + tile` receives the plan
+__device__ __forceinline__ void make_tile_plan_range(const DevParams& p, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ lb,
+                                                     uint32_t tile, uint32_t i0, uint32_t i1, TilePlan* __restrict__ plans) {
     constexpr int NI = SPH_MAX_ROWS * 3;
-    const uint32_t i0 = p.own_begin + tile * SPH_THREADS;
-    const uint32_t i1 = min(i0 + SPH_THREADS, p.own_begin + p.n);
     const uint32_t kf = min(__ldg(keys + i0), p.num_cells - 1u), kl = min(__ldg(keys + i1 - 1u), p.num_cells - 1u);
     const uint32_t yf = kf / p.grid_w, xa = kf - yf * p.grid_w;
     const uint32_t yl = kl / p.grid_w, xb = kl - yl * p.grid_w;
@@ -125,6 +124,11 @@ __device__ __forceinline__ void make_tile_plan(const DevParams& p, const uint32_
     uint4* dst = reinterpret_cast<uint4*>(plans + tile);
 #pragma unroll
     for (int q = 0; q < 4; q++) dst[q] = src[q];
+}
+__device__ __forceinline__ void make_tile_plan(const DevParams& p, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ lb,
+                                               uint32_t tile, TilePlan* __restrict__ plans) {
+    const uint32_t i0 = p.own_begin + tile * SPH_THREADS;
+    make_tile_plan_range(p, keys, lb, tile, i0, min(i0 + SPH_THREADS, p.own_begin + p.n), plans);
 }
 
 __global__ void __launch_bounds__(128)
@@ -302,15 +306,19 @@ __device__ __forceinline__ float density_walk_staged(const DevParams& p, uint32_
 __global__ void __launch_bounds__(SPH_THREADS)
 k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* __restrict__ keys,
           const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk, float* __restrict__ rho,
-          uint32_t* __restrict__ wild_stamp /* null: slab mode */, const uint32_t* __restrict__ frame_time,
-          const TilePlan* __restrict__ plans) {
+          uint32_t* __restrict__ wild_stamp, const uint32_t* __restrict__ frame_time,
+          const TilePlan* __restrict__ plans,
+          const uint32_t* __restrict__ band_range /* multi-GPU band: {first, end} of the particles to compute, on the device; tiles count from 0. Else null */) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP + 2];  // + pad: the pair loop may load one record past a span
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
     pdl_enter();
-    // slab mode: owned particles are [own_begin, own_begin + n) of arrays that also hold halo rows on both sides
-    const uint32_t i0 = p.own_begin + blockIdx.x * SPH_THREADS;
-    const uint32_t i1 = min(i0 + SPH_THREADS, p.own_begin + p.n);
+    // band mode (kernels_band.cuh): the key-ordered arrays hold [ghost rows | owned | ghost rows]; density is computed for
+    // the owned particles and one ghost row on each side, a range only the device knows
+    const uint32_t r_begin = band_range ? __ldg(band_range) : p.own_begin;
+    const uint32_t r_end = band_range ? __ldg(band_range + 1) : p.own_begin + p.n;
+    const uint32_t i0 = (band_range ? 0u : p.own_begin) + blockIdx.x * SPH_THREADS;
+    if (i0 + SPH_THREADS <= r_begin || i0 >= r_end) return;  // (whole CTA; never true on a single GPU)
     if (threadIdx.x == 0) {
         mbar_init(&s_bar, 1);
         mbar_fence_init();
@@ -320,7 +328,7 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
         stage_from_plan<1>(plans + blockIdx.x, arrays, smem, eb, &s_bar, &s_plan);
     }
     const uint32_t i = i0 + threadIdx.x;
-    const bool valid = i < p.own_begin + p.n;
+    const bool valid = i >= r_begin && i < r_end;
     uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
     float2 me = make_float2(0.f, 0.f);
     uint32_t cy = 0;
@@ -839,7 +847,8 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
                   const TilePlan* __restrict__ plans,
                   float2* __restrict__ pos_out, float2* __restrict__ vel_out, float2* __restrict__ dbg_accel,
                   float2* __restrict__ dbg_abs,
-                  uint32_t* __restrict__ next_keys /* null: do not speculate */, uint32_t* __restrict__ next_count) {
+                  uint32_t* __restrict__ next_keys /* null: do not speculate */, uint32_t* __restrict__ next_count,
+                  const uint32_t* __restrict__ band_range /* multi-GPU band: {first, end} of the owned particles, on the device; else null */) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP];
     __shared__ __align__(128) float2 s_vel[SPH_CAP];
     __shared__ __align__(128) float s_rho[SPH_CAP];
@@ -847,9 +856,11 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
     pdl_enter();
-    // slab mode: owned particles are [own_begin, own_begin + n) of arrays that also hold halo rows on both sides
-    const uint32_t i0 = p.own_begin + blockIdx.x * SPH_THREADS;
-    const uint32_t i1 = min(i0 + SPH_THREADS, p.own_begin + p.n);
+    // band mode: owned particles are [first, end) of arrays that also hold ghost rows on both sides (see k_density)
+    const uint32_t r_begin = band_range ? __ldg(band_range) : p.own_begin;
+    const uint32_t r_end = band_range ? __ldg(band_range + 1) : p.own_begin + p.n;
+    const uint32_t i0 = (band_range ? 0u : p.own_begin) + blockIdx.x * SPH_THREADS;
+    if (i0 + SPH_THREADS <= r_begin || i0 >= r_end) return;  // (whole CTA; never true on a single GPU)
     if (threadIdx.x == 0) {
         mbar_init(&s_bar, 1);
         mbar_fence_init();
@@ -859,7 +870,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
         stage_from_plan<3>(plans + blockIdx.x, arrays, smem, eb, &s_bar, &s_plan);
     }
     const uint32_t i = i0 + threadIdx.x;
-    const bool valid = i < p.own_begin + p.n;
+    const bool valid = i >= r_begin && i < r_end;
     uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
     float2 pos = make_float2(0.f, 0.f), pred = pos, vel = pos;
     float dens = 1.0f;
@@ -873,7 +884,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     }
     const uint32_t ft = __ldg(frame_time);
     const bool tame = wild_stamp != nullptr && __ldg(wild_stamp) != ft;  // common.cuh tame_component
-    const uint32_t out_i = i - p.own_begin;                      // index in the (halo-free) state arrays
+    const uint32_t out_i = i - r_begin;                          // index in the (ghost-free) state arrays
     const uint32_t goff = p.global_offset + (global_offset_dev ? __ldg(global_offset_dev) : 0u);
     uint32_t rand_seed = (out_i + goff) * 12u + ft * 69u;  // compute.wgsl:161 (global sorted index)
     const float pressure = fmul(p.pressure_constant, fsub(dens, p.rest_density));

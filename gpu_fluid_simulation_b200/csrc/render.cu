@@ -93,7 +93,7 @@ extern "C" int fluid_sim_render(FluidSim* h_, const float inv_proj[16], uint32_t
     if (!h_ || !inv_proj || (!rgba_f32_out && !rgba8_out)) { set_error("fluid_sim_render: null argument"); return FLUID_ERR_INVALID_ARGUMENT; }
     if (w == 0 || h == 0 || w > 16384 || h > 16384) { set_error("fluid_sim_render: bad image size"); return FLUID_ERR_INVALID_ARGUMENT; }
     Sim* s = reinterpret_cast<Sim*>(h_);
-    if (s->slab) { set_error("fluid_sim_render: not available on a slab handle (gather the bands first)"); return FLUID_ERR_UNSUPPORTED; }
+    if (s->band) { set_error("fluid_sim_render: not available on a band of a FluidMulti (gather the bands first)"); return FLUID_ERR_UNSUPPORTED; }
     FLUID_CUDA(cudaSetDevice(s->device));
     const size_t npx = (size_t)w * h;
     float4* d_f = nullptr;

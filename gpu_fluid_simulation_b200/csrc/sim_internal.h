@@ -1,7 +1,6 @@
 // sim_internal.h — the state behind the opaque FluidSim handle.
 #pragma once
 #include "common.cuh"
-#include "slab_rows.h"
 
 namespace fluid {
 
@@ -75,23 +74,11 @@ struct Sim {
     bool debug_force = false;
     bool exact_math = true;   // FLUID_MATH_EXACT / FLUID_MATH_FAST
 
-    // slab (multi-GPU) mode, kernels_slab.cuh / slab.inl
-    bool slab = false;
-    uint32_t slab_pad = 0, slab_capacity = 0;
-    uint32_t state_off = 0;    // index of the first native in pos_a / vel_a / keys_u
-    uint32_t sorted_off = 0;   // index of the first owned particle in pos_s / pred_s / vel_s / rho / keys_ext
-    SlabRows slab_rows{};
-    uint32_t* keys_ext = nullptr;              // keys of [halo | owned | halo]
-    unsigned long long* emig_list = nullptr;   // (destination rank << 32) | index in the state arrays
-    uint32_t* emig_count = nullptr;
-    uint32_t emig_cap = 0;
-    uint32_t* slab_meta = nullptr;
-    DevParams slab_params{};
-    uint32_t* slab_bin_lb = nullptr;          // counting sort of a band: exclusive scan over its cells + the sentinel bin
-    uint32_t slab_bins = 0, slab_bin_tiles = 0;
-    bool slab_counting = true;                // FLUID_SLAB_RADIX=1: radix passes always
-    uint32_t* slab_dyn = nullptr;             // SlabDyn (kernels_slab.cuh), device-resolved protocol
-    const uint32_t* slab_goff_dev = nullptr;  // &slab_dyn->global_offset while that protocol is in use, else null
+    // a band of the multi-GPU step (kernels_band.cuh / multi.inl): the handle is owned by a FluidMulti
+    bool band = false;
+    uint32_t state_off = 0;    // index of the first owned particle in pos_a / vel_a (always 0)
+    uint32_t sorted_off = 0;   // index of the first owned particle in pos_s / pred_s / vel_s / rho / sorted keys (band: set by a download)
+    uint32_t* lb_view = nullptr;  // the lower-bound table as the neighbour passes index it (by global cell id): cell_lb, or a band's table shifted by its first cell
 
     uint32_t *jfa_a = nullptr, *jfa_b = nullptr;  // packed seed ping-pong for fluid_sim_jfa_from_particles
     size_t jfa_pixels = 0;
@@ -114,7 +101,7 @@ struct Sim {
     DevParams make_params(const FluidSimUniform& u) const;
     void mark(const char* name);
     int enqueue_tick(const FluidTickSettings& t, bool hash_sort_only);
-    uint32_t* keys_view() const { return slab ? keys_ext + sorted_off : keys_sorted; }
+    uint32_t* keys_view() const { return keys_sorted + sorted_off; }
 };
 
 }  // namespace fluid

@@ -15,7 +15,7 @@ _M = (1 << 64) - 1
 
 def splitmix64(seed: int, count: int, start: int = 0) -> np.ndarray:
     """draws start .. start+count-1 of the splitmix64 stream as doubles in [0,1) (state_i = seed + (i+1)*golden, so any
-    sub-range can be generated on its own: each rank of a slab run builds only its band)."""
+    sub-range can be generated on its own: each rank of a multi-GPU run builds only its band)."""
     with np.errstate(over="ignore"):
         i = np.arange(start + 1, start + count + 1, dtype=np.uint64)
         z = np.uint64(seed & _M) + i * np.uint64(0x9E3779B97F4A7C15)
@@ -57,13 +57,23 @@ def uniform_box(n_side: int, spacing=0.1, h=0.2, tex=(1024, 1024), lattice_rows=
     return settings, TickSettings(), p
 
 
-def dam_break(cols: int, rows: int, spacing=0.1, h=0.2, tex=(1024, 1024)):
-    """Scene D: cols x rows jittered block against the left wall of a box 4x as wide; gravity (0, 9.8)."""
+def dam_break(cols: int, rows: int, spacing=0.1, h=0.2, tex=(1024, 1024), lattice_rows=None):
+    """Scene D: cols x rows jittered block against the left wall of a box 4x as wide; gravity (0, 9.8).
+    lattice_rows=(r0, r1): only the particles of lattice rows r0..r1-1 (a contiguous range of the full array)."""
     size = (cols * spacing * 4.0, rows * spacing)
     settings = SimulationSettings(particle_count=cols * rows, particle_spacing=spacing, smoothing_radius=h,
                                   size=size, texture_size=tex)
-    p = _block(cols, rows, spacing, -size[0] / 2, -size[1] / 2, 0.25, 0.0)
+    r0, r1 = (0, rows) if lattice_rows is None else lattice_rows
+    p = _block(cols, rows, spacing, -size[0] / 2, -size[1] / 2, 0.25, 0.0, r0 * cols, r1 * cols)
     return settings, TickSettings(gravity=(0.0, 9.8)), p
+
+
+def band_lattice_rows(row_bounds, rank, n_lattice_rows):
+    """lattice rows of scene U / D that lie in the grid rows [row_bounds[rank], row_bounds[rank+1]): with spacing = h/2 and
+    jitter < spacing/2, lattice rows 2k and 2k+1 lie in grid row k+1 (grid row 0 is the empty border row)."""
+    lo, hi = max(row_bounds[rank], 1), max(row_bounds[rank + 1], 1)
+    r0, r1 = min(2 * (lo - 1), n_lattice_rows), min(2 * (hi - 1), n_lattice_rows)
+    return r0, max(r0, r1)
 
 
 def assert_no_coincident(p: np.ndarray):

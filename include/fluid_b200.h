@@ -25,14 +25,15 @@
 extern "C" {
 #endif
 
-#define FLUID_B200_ABI_VERSION 1
+#define FLUID_B200_ABI_VERSION 2
 
 typedef enum FluidStatus {
     FLUID_OK = 0,
     FLUID_ERR_INVALID_ARGUMENT = -1, /* null pointer, particle_count < 2, bad sizes */
     FLUID_ERR_CUDA = -2,             /* a CUDA runtime call failed; see fluid_last_error */
     FLUID_ERR_NO_DEVICE = -3,        /* no CUDA device / ordinal out of range */
-    FLUID_ERR_UNSUPPORTED = -4       /* e.g. image larger than the JFA seed encoding allows */
+    FLUID_ERR_UNSUPPORTED = -4,      /* e.g. image larger than the JFA seed encoding allows; NCCL not loadable */
+    FLUID_ERR_OVERFLOW = -5          /* multi-GPU step: an exchange window or a band's capacity overflowed (particles lost) */
 } FluidStatus;
 
 /* reference: `ParticleInstance`, src/simulation.rs:126-135 (WGSL twin funcs.wgsl:1-8).
@@ -153,7 +154,7 @@ int fluid_sim_get_math_mode(const FluidSim* sim);
  * FLUID_SORT_RADIX: onesweep LSD radix passes over (key, index); cost independent of the distribution.
  * FLUID_SORT_AUTO (default): counting while the most crowded cell holds <= clamp(n / 1024, 64, 4096) particles and the
  *   squared cell populations sum to <= 128 n (both watched per tick without a sync; one stream sync on the first tick
- *   after an upload), radix otherwise. Slab mode always uses the radix passes.
+ *   after an upload), radix otherwise. The bands of the multi-GPU step always count (ranked by origin, see fluid_multi_*).
  * fluid_sim_last_sort_path: which of the two the most recently enqueued tick used. */
 #define FLUID_SORT_AUTO 0
 #define FLUID_SORT_RADIX 1
@@ -181,8 +182,7 @@ int fluid_sim_upload_particles(FluidSim* sim, const FluidParticle* src);
  * Copies run on the handle's own copy streams through separate staging buffers, ordered against the tick stream by
  * events: the upload of the next state overlaps the download of the previous result. `src` / `dst` should be pinned
  * (pageable memory degrades to synchronous copies) and must stay untouched until fluid_sim_sync_transfers returns or,
- * for `src`, until the next _upload_particles_async on the same handle has been issued AND a later sync returned.
- * Not available in slab mode. */
+ * for `src`, until the next _upload_particles_async on the same handle has been issued AND a later sync returned. */
 int fluid_sim_upload_particles_async(FluidSim* sim, const FluidParticle* src);
 int fluid_sim_download_particles_async(FluidSim* sim, FluidParticle* dst);
 int fluid_sim_sync_transfers(FluidSim* sim);
@@ -239,52 +239,79 @@ uint64_t fluid_sim_launch_count(const FluidSim* sim);
 int fluid_sim_reserve(FluidSim* sim, uint32_t capacity);
 int fluid_sim_set_particle_count(FluidSim* sim, uint32_t n);
 
-/* ---- slab (multi-GPU) mode: SURVEY.md §8(e) -------------------------------------------
- * One handle per rank owns a band of grid rows [row_bounds[rank], row_bounds[rank+1]). Keys stay global. The host
- * drives the phases below and performs the three exchanges between them (migration, halo pred+vel, halo rho) with
- * NCCL on views of the handle's device arrays (FluidSlabView); see gpu_fluid_simulation_b200/slab.py. The reference
- * has no multi-GPU code; the contract is that the gathered result equals a single-GPU tick of the same state. */
-typedef struct FluidSlabView {
-    uint32_t n;            /* particles currently owned */
-    uint32_t pad;          /* state arrays: natives start at index pad; key-ordered arrays: owned start at pad */
-    uint32_t capacity;
-    uint32_t emig_cap;
-    void* pos_state;       /* float2[pad + capacity + pad] */
-    void* vel_state;
-    void* pos_sorted;      /* float2[...] key order, [halo below | owned | halo above] around index pad */
-    void* pred_sorted;
-    void* vel_sorted;
-    void* rho;             /* float[...] */
-    void* keys_ext;        /* uint32[...] */
-    void* emig_list;       /* uint64[emig_cap]: (destination rank << 32) | index into the state arrays; 0xff.. = unused */
-    void* emig_count;      /* uint32; emig_count[8 + r] = emigrants bound for rank r */
-    void* meta;            /* uint32[5]: n owned, first-row count, last-row count, key of first owned, its start_indices entry */
-    void* start_indices;   /* uint32[grid_w*grid_h], global sorted indices for the cells this rank owns */
-    void* dyn;             /* uint32[8]: hb, ha, ext_begin, ext_end, global_offset, quirk c0, quirk stale, error bits */
-} FluidSlabView;
-int fluid_slab_configure(FluidSim* sim, int rank, int world, const uint32_t* row_bounds /* world+1 */, uint32_t capacity,
-                         uint32_t pad, uint32_t emig_cap);
-int fluid_slab_view(FluidSim* sim, FluidSlabView* out);
-/* phase 1: tick += 1; keys of the natives; emigrants listed and given the sentinel key */
-int fluid_slab_begin_tick(FluidSim* sim, const FluidTickSettings* tick);
-/* phase 2a: sort the emigrant list (destination rank, then source order) and gather (pos, vel) of the n_emigrants
- * into payload_dev (DEVICE pointer, float[n_emigrants*4]); 2b: place the received immigrants (DEVICE pointer,
- * ordered by source rank: n_from_below then n_from_above records) around the natives */
-int fluid_slab_pack(FluidSim* sim, uint32_t n_emigrants, float* payload_dev);
-int fluid_slab_unpack(FluidSim* sim, const float* recv_dev, uint32_t n_from_below, uint32_t n_from_above);
-/* phase 3+4: keys of the immigrants (already copied in around the natives), sort, gather, band metadata */
-int fluid_slab_sort(FluidSim* sim, uint32_t n_from_below, uint32_t n_from_above, uint32_t n_emigrants);
-/* phase 6+7a: halo keys, cell tables, density. quirk_*: lowest occupied cell of the whole domain and its stale
- * start_indices entry translated to this rank's key-ordered index space (0xffffffff, 0 when not visible) */
-int fluid_slab_cells_density(FluidSim* sim, uint32_t halo_below, uint32_t halo_above, uint32_t global_offset,
-                             uint32_t quirk_c0, uint32_t quirk_stale_ext);
-/* phases 6+7a without a host read: allmeta_dev = DEVICE pointer to world x 8 uint32 (every rank's `meta` words, as
- * gathered by the exchange layer). Halo rows must have been received as pad-sized windows (below: right-aligned at
- * the owned range; above: starting right after it); halo counts, global offset and the quirk are resolved on the
- * device. FluidSlabView.dyn[7] latches error bits (1: a halo row exceeds the pad). */
-int fluid_slab_cells_density_dev(FluidSim* sim, const uint32_t* allmeta_dev);
-/* phase 7b: force + integrate of the owned particles */
-int fluid_slab_force(FluidSim* sim);
+/* ---- the multi-GPU step: SURVEY.md §8(e) ------------------------------------------------------------------------------
+ * The domain is cut into bands of grid rows, one band per GPU ("rank"); keys stay global. The reference has no multi-GPU
+ * code; its caller makes one call per frame, `FluidSimulation::tick` (src/simulation.rs:459, from src/renderer.rs:415-418),
+ * and so does a caller of this block: fluid_multi_tick enqueues the whole step of every band this process drives — kernels
+ * and the tick's single exchange (the boundary rows' particles as ghosts + the particles that changed bands, in one
+ * fixed-size window per pair of ranks) — and returns without reading anything back: counts, offsets and halo sizes stay on
+ * the device. The contract: the bands, concatenated in rank order, are bit for bit the state a single FluidSim holds after
+ * the same ticks (same keys, same order inside a cell, same floats, same start_indices).
+ *   fluid_multi_create       one process drives all ranks (one host thread; what a Rust `FluidSimulation::new_multi` binds)
+ *   fluid_multi_create_rank  one rank per process (torchrun / mpirun style); the ranks share fluid_multi_unique_id's bytes
+ * Errors that only the device can see (an exchange window or a band's capacity overflowed) are latched there and reported
+ * as FLUID_ERR_OVERFLOW by the next call that synchronises (fluid_multi_sync, downloads). */
+#define FLUID_TRANSPORT_AUTO 0   /* NCCL when every rank has its own GPU, LOCAL when ranks share one */
+#define FLUID_TRANSPORT_NCCL 1   /* one ncclGroup of send/recv windows per tick (NCCL over NVLink / NVSwitch) */
+#define FLUID_TRANSPORT_LOCAL 2  /* ranks of ONE process: pull kernels over peer-mapped (or the same GPU's) memory, ordered by events */
+#define FLUID_MULTI_MAX_RANKS 8
+#define FLUID_MULTI_ID_BYTES 128 /* sizeof(ncclUniqueId) */
+typedef struct FluidMultiOptions {
+    uint32_t row_bounds[FLUID_MULTI_MAX_RANKS + 1]; /* rank r owns grid rows [row_bounds[r], row_bounds[r+1]); all zero: equal bands */
+    uint32_t capacity;     /* particles a rank can own; 0: particle_count / ranks * 1.25 + 4096 */
+    uint32_t window_near;  /* records per exchange window between adjacent ranks (2 ghost rows + migrants each way); 0: max(16 x average row, 8192) */
+    uint32_t window_far;   /* records per window between non-adjacent ranks (long jumps: the force-field push-out, compute.wgsl:131-136); 0: 1024 */
+    int32_t transport;     /* FLUID_TRANSPORT_* */
+    uint32_t reserved[4];
+} FluidMultiOptions;
+typedef struct FluidMulti FluidMulti; /* opaque */
+
+/* reference: `FluidSimulation::new` (src/simulation.rs:139) on n_ranks GPUs: devices[r] = CUDA ordinal of rank r (the same
+ * ordinal may repeat with FLUID_TRANSPORT_LOCAL: several bands on one GPU). Builds the init lattice of :147-163. opt may be NULL. */
+int fluid_multi_create(const FluidSimSettings* settings, int n_ranks, const int* devices, const FluidMultiOptions* opt, FluidMulti** out);
+/* one rank per process: rank 0 makes the id, the launcher hands the same bytes to every rank. The bands start empty. */
+int fluid_multi_unique_id(uint8_t out[FLUID_MULTI_ID_BYTES]);
+int fluid_multi_create_rank(const FluidSimSettings* settings, int rank, int world, const uint8_t id[FLUID_MULTI_ID_BYTES], int device,
+                            const FluidMultiOptions* opt, FluidMulti** out);
+void fluid_multi_destroy(FluidMulti* m);
+/* reference: `FluidSimulation::tick` (src/simulation.rs:459-539); asynchronous on every band's stream */
+int fluid_multi_tick(FluidMulti* m, const FluidTickSettings* tick);
+int fluid_multi_tick_n(FluidMulti* m, const FluidTickSettings* tick, uint32_t n);
+/* reference: `device.poll(Wait)` (src/main.rs:79); returns FLUID_ERR_OVERFLOW if a rank latched an error */
+int fluid_multi_sync(FluidMulti* m);
+uint32_t fluid_multi_tick_count(const FluidMulti* m);
+int fluid_multi_set_tick_count(FluidMulti* m, uint32_t tick);
+int fluid_multi_set_math_mode(FluidMulti* m, int mode);
+int fluid_multi_world(const FluidMulti* m);
+int fluid_multi_local_bands(const FluidMulti* m); /* bands this process drives: world, or 1 */
+int fluid_multi_transport(const FluidMulti* m);
+int fluid_multi_row_bounds(const FluidMulti* m, uint32_t* out /* world + 1 */);
+/* binding 0 of simulation_bg for the whole domain: N x 32 B AoS in the global array order (upload; it fixes the order of
+ * particles that share a cell, as on one GPU) / in global key order (download). Handles that drive all ranks. */
+int fluid_multi_upload_particles(FluidMulti* m, const FluidParticle* all, uint32_t n);
+int fluid_multi_download_particles(FluidMulti* m, FluidParticle* dst);
+/* one rank per process. upload: COLLECTIVE; each rank passes any subset of the scene (the first tick moves every particle to
+ * the rank that owns its row); origins = the particles' indices in the global array, NULL = the ranks' subsets
+ * concatenated in rank order. download: the band in key order, its size and its offset in the global key order. */
+int fluid_multi_upload_band(FluidMulti* m, const FluidParticle* band, uint32_t n, const uint32_t* origins);
+int fluid_multi_download_band(FluidMulti* m, int local_band, FluidParticle* dst, uint32_t cap, uint32_t* n_out, uint32_t* global_offset_out);
+/* synchronises; counts[r] = particles rank r owns (every rank tracks all of them on the device) */
+int fluid_multi_particle_counts(FluidMulti* m, uint32_t* counts /* world */);
+/* bindings 1 and 2 for the whole domain (start_indices holds GLOBAL sorted indices; one-rank-per-process handles return
+ * their own table: valid for the rows they own) */
+int fluid_multi_download_start_indices(FluidMulti* m, uint32_t* dst);
+int fluid_multi_upload_start_indices(FluidMulti* m, const uint32_t* src);
+int fluid_multi_upload_force_field(FluidMulti* m, const float* xy);
+/* per-phase device timing of one local band (as fluid_sim_last_timing); kernels launched by all local bands */
+int fluid_multi_enable_timing(FluidMulti* m, int enable);
+int fluid_multi_last_timing(FluidMulti* m, int local_band, const char** names, float* ms, int cap);
+uint64_t fluid_multi_launch_count(const FluidMulti* m);
+void* fluid_multi_stream(FluidMulti* m, int local_band); /* cudaStream_t */
+/* the FluidSim behind a local band, for read-only queries (device view, uniform); it cannot be ticked on its own */
+FluidSim* fluid_multi_band_sim(FluidMulti* m, int local_band);
+/* row bounds that give every rank (nearly) the same number of particles, from the positions (scenes whose rows are
+ * unevenly filled: the dam break); out: world + 1 entries for FluidMultiOptions.row_bounds. Host arithmetic only. */
+int fluid_multi_balanced_bounds(const FluidSimSettings* settings, const FluidParticle* particles, uint32_t n, int world, uint32_t* out);
 
 /* ---- jump-flood distance field (reference: shaders/jump_flood.wgsl:17-65; the host
  *      protocol is pinned in SURVEY.md §8 row a7) ---------------------------------- */
