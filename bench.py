@@ -130,19 +130,36 @@ def host_cores():
         return os.cpu_count() or 1
 
 
-def run_cpu(workload, ticks, warmup=1, budget_s=25.0, full=False):
-    """times the CPU oracle (port of the reference's WGSL step; counting sort = the fair CPU variant) on every host core."""
+def run_cpu(workload, ticks, warmup=1, budget_s=25.0, full=False, kind="auto"):
+    """times the reference's step on every host core.
+    kind "reference": the reference's own WGSL shaders (compute.wgsl + funcs.wgsl, sort.wgsl), transpiled mechanically to
+      C++ (oracle/transpile_wgsl.py -> oracle/_ref/libwgsl_ref.so) and dispatched as src/simulation.rs:512-537 records them:
+      S(S+1)/2 bitonic passes over whole records, the 7x7 density walk, two 3x3 walks in move_particle. OpenMP over invocations.
+    kind "port": the hand-written oracle with a stable counting sort (a fair CPU algorithm, not the reference's).
+    kind "auto": "reference" when the transpiled library is there, else "port"."""
     from oracle import oracle as O
+    from oracle import wgsl_ref as W
     O.build()
-    O.lib().oracle_set_num_threads(host_cores())
+    if kind == "auto":
+        kind = "reference" if W.available() else "port"
+    cores = host_cores()
+    O.lib().oracle_set_num_threads(cores)
     (s, ts, p), desc = cpu_sample_scene(workload, full)
-    sim = O.OracleSim(s, p, sort_mode=O.SORT_COUNTING)
+    if kind == "reference":
+        W.lib().wgslref_set_num_threads(cores)
+        sim = W.WgslRefSim(O, s, p)
+        how = ("the reference's WGSL transpiled to C++ (oracle/_ref), its own dispatch schedule (bitonic network, 7x7 density walk), "
+               f"OpenMP over invocations on {cores} threads")
+    else:
+        sim = O.OracleSim(s, p, sort_mode=O.SORT_COUNTING)
+        how = f"oracle port, OpenMP over particles on {cores} threads, stable counting sort"
+    del p
     t_w = time.perf_counter()
     warm_done = 0
     for _ in range(warmup):
         sim.tick(ts)
         warm_done += 1
-        if budget_s and time.perf_counter() - t_w > 0.4 * budget_s:
+        if budget_s and time.perf_counter() - t_w > 0.25 * budget_s:
             break
     t0 = time.perf_counter()
     done = 0
@@ -153,29 +170,26 @@ def run_cpu(workload, ticks, warmup=1, budget_s=25.0, full=False):
             break
     dt = time.perf_counter() - t0
     n = s.particle_count
-    return {"value": n * done / dt, "unit": "particle-steps/s", "cores": int(O.lib().oracle_num_threads()), "kind": "port",
-            "sample": f"{done} ticks (after {warm_done} warm-up) of {desc}; OpenMP over particles on {int(O.lib().oracle_num_threads())} "
-                      "threads, stable counting sort", "ms_per_step": 1e3 * dt / done,
+    return {"value": n * done / dt, "unit": "particle-steps/s", "cores": cores, "kind": kind,
+            "sample": f"{done} ticks (after {warm_done} warm-up) of {desc}; {how}", "ms_per_step": 1e3 * dt / done,
             "particles": n, "ticks": done, "warmup": warm_done}
 
 
 def reference_arm(args, rank):
-    """--impl reference: the reference's step on the host cores. The reference has no CPU implementation of this path
-    and its WGSL cannot run here, so this is the oracle port (kind "port"), on the NAMED workload when a tick of it is
-    affordable (64M: ~5 s per tick on 32 cores), else on the 1M-particle sample (config.particles says which)."""
+    """--impl reference: the reference's own step on the host cores. Its WGSL cannot run through a graphics API on this box;
+    what runs is that same WGSL transpiled to C++ (kind "reference"; the hand-written port if the transpiled library is
+    missing), on the NAMED workload (config.same_config), every step one full tick; steps / warm-up are cut short when the
+    time budget runs out (a 64M-particle tick of the reference's 351-pass bitonic network takes tens of seconds on a CPU)."""
     if rank != 0:
         return
-    n_named = {"uniform": lambda a: a * a, "dam": lambda a: a[0] * a[1], "default": lambda a: 100_000}[WORKLOADS[args.workload][0]](WORKLOADS[args.workload][1])
-    full = os.environ.get("FLUID_REF_SAMPLE", "") != "1" and (n_named <= 4_000_000 or (host_cores() >= 8 and args.steps <= 64))
-    steps = args.steps
-    r = run_cpu(args.workload, steps, warmup=args.warmup, budget_s=150.0, full=full)
+    full = os.environ.get("FLUID_REF_SAMPLE", "") != "1"
+    r = run_cpu(args.workload, args.steps, warmup=args.warmup, budget_s=150.0, full=full)
     line = {"impl": "reference", "metric": "particle-steps/sec", "value": r["value"], "unit": "particle-steps/s",
             "n_gpus": args.gpus, "steps": r["ticks"], "warmup": r["warmup"], "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "particles": r["particles"], "same_config": bool(full),
-                       "note": "CPU oracle (C++ restatement of the reference's WGSL step; the reference's own wgpu/WGSL path is "
-                               "unavailable on this box); every step is one full tick" + ("" if full else " of a bounded 1M-particle sample of the workload")
-                               + "; steps / warm-up are cut short when the time budget (150 s + 60 s) runs out"},
+                       "note": "the reference's step on the host cores (its wgpu/WGSL path through a graphics API is unavailable on this "
+                               "box): " + r["sample"]},
             "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": r["value"], "unit": "particle-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -381,8 +395,10 @@ def main():
     cpu = None
     if not args.no_cpu_baseline:
         sim.close()
-        cpu = run_cpu(args.workload, 8, warmup=1, budget_s=20.0)
+        cpu = run_cpu(args.workload, 8, warmup=1, budget_s=12.0)
+        port = run_cpu(args.workload, 8, warmup=1, budget_s=8.0, kind="port") if cpu["kind"] != "port" else cpu
         cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        cpu["port"] = {k: port[k] for k in ("value", "sample")}  # the same step with a fair CPU sort (hand-written oracle)
 
     line = {"metric": "particle-steps/sec", "value": value, "unit": "particle-steps/s", "n_gpus": 1, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",

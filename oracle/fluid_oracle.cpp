@@ -7,15 +7,17 @@
 // as the checker or the timed CPU baseline. The product (libfluid_b200.so) never
 // links, loads or calls it.
 //
-// PARITY UNPINNED: the reference has no tests, golden vectors or fixtures
-//  and cannot be built or run in this environment (no rustc/cargo,
-// no graphics API for the WGSL). This oracle is pinned instead by (a) the
-// restatement rules of SURVEY.md §8(c): IEEE-754 binary32, round-to-nearest-even,
-// no FMA contraction (build with -ffp-contract=off), correctly rounded / and sqrt,
-// pow(h,8) evaluated with powf, out-of-range cells empty, out-of-range texel index
-// clamped to the last texel, Jacobi reads in move_particle; and (b) the self-checks
-// in tests/test_oracle.py (bitonic keys == sorted keys, 7x7 vs 3x3 density walk,
-// fp64 brute force, default-scene invariants, JFA vs brute force).
+// PARITY: the reference has no tests, golden vectors or fixtures and cannot be built or run in this
+// environment (no rustc/cargo, no graphics API for the WGSL), so no reference-held vector pins this file. It is
+// pinned by (a) a second, MECHANICAL derivation: oracle/transpile_wgsl.py rewrites the reference's WGSL text into C++
+// (oracle/_ref/libwgsl_ref.so), and tests/test_wgsl_ref.py compares every pass, whole ticks, the bitonic network
+// (incl. its tie order) and the jump-flood pass bit for bit with this restatement; (b) the restatement rules of
+// IEEE-754 binary32, round-to-nearest-even, no FMA contraction (build with -ffp-contract=off),
+// correctly rounded / and sqrt, pow(h,8) evaluated with powf, out-of-range cells empty, out-of-range texel index
+// clamped to the last texel, Jacobi reads in move_particle; and (c) the self-checks in tests/test_oracle.py (bitonic
+// keys == sorted keys, 7x7 vs 3x3 density walk, fp64 brute force, default-scene invariants, JFA vs brute force).
+// What stays restated by hand only: the Rust host parts (uniform derivation, init lattice, bitonic schedule,
+// generate_smooth_gradient_field) and the two render shaders (render_oracle.cpp).
 //
 // Build: see oracle/Makefile (g++ -O2 -ffp-contract=off -fopenmp -shared -fPIC).
 

@@ -2,7 +2,9 @@
 
 TEST INFRASTRUCTURE: the checker for tests/, __graft_entry__.smoke() and bench.py's cpu_baseline and
 `--impl reference` legs. Nothing in gpu_fluid_simulation_b200/ imports this module.
-PARITY UNPINNED (no reference tests / golden vectors exist; see fluid_oracle.cpp header).
+PARITY: the reference has no tests or golden vectors and cannot run here; this restatement is pinned instead by a second,
+mechanical derivation — the reference's WGSL transpiled to C++ (oracle/transpile_wgsl.py, oracle/wgsl_ref.py) — against which
+tests/test_wgsl_ref.py compares it bit for bit. The Rust host parts (uniform, lattice, CPU field) remain restated by hand.
 """
 import ctypes as C
 import os

@@ -90,18 +90,15 @@ inline vec2<float> floor(vec2<float> a) { return {floorf(a.x), floorf(a.y)}; }
 inline float max(float a, float b) { return a < b ? b : a; }  // WGSL: b if a < b else a
 template <class T> inline T select(T f, T t, bool c) { return c ? t : f; }
 
-// ---- storage: runtime-sized arrays with robust buffer access (an out-of-bounds read yields zero, an out-of-bounds
-// write is discarded: one of the behaviours WebGPU allows; SURVEY.md §8(c) pins "cells outside the grid are empty",
-// which this reproduces: no particle carries an out-of-range key) ----
+// ---- storage: runtime-sized arrays with robust buffer access. WebGPU lets an out-of-bounds access be clamped to an
+// in-bounds element; SURVEY.md §8(c) pins exactly that for the force-field texel (compute.wgsl:129 at uv == 1.0 on the
+// last row) and "cells outside the grid are empty" for start_indices — which clamping also gives: the entry it returns
+// points at a particle whose key is not the out-of-range cell id, so the walk stops at once. No shader of the path
+// STORES out of bounds (keys < cells, ids < n, sort.wgsl:39-41 checks index_high). ----
 template <class T> struct Storage {
     T* data = nullptr;
     uint32_t len = 0;
-    T& operator[](uint32_t i) {
-        if (i < len) return data[i];
-        static thread_local T scratch;
-        scratch = T();
-        return scratch;
-    }
+    T& operator[](uint32_t i) { return data[i < len ? i : len - 1u]; }
 };
 // rg32uint storage textures (jump_flood.wgsl): textureLoad returns (r, g, 0, 1); textureStore writes r, g
 struct Texture2D {
