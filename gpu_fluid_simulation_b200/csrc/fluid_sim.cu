@@ -221,17 +221,23 @@ void launch_tile_plans(Sim* s, const DevParams& p, const uint32_t* keys, bool pd
 
 void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, float2* vel_out, bool pdl = false,
                   uint32_t* next_keys = nullptr, uint32_t* next_count = nullptr, const uint32_t* band_range = nullptr,
-                  const uint32_t* goff_dev = nullptr) {
+                  const uint32_t* goff_dev = nullptr, const BandSpec* band_spec = nullptr) {
     float2* da = s->debug_force ? s->dbg_accel : nullptr;
     float2* db = s->debug_force ? s->dbg_abs : nullptr;
     const uint32_t* keys = s->keys_sorted;
 #define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                     \
-    launch_pdl(pdl, k_force_integrate<DBG, EX>, dim3(blocks), dim3(SPH_THREADS), s->stream, p, s->pos_s, s->pred_s, s->vel_s, \
+    launch_pdl(pdl, k_force_integrate<DBG, EX, false>, dim3(blocks), dim3(SPH_THREADS), s->stream, p, s->pos_s, s->pred_s, s->vel_s, \
                s->rho, keys, s->lb_view, s->quirk, s->force_field, s->d_frame_time, goff_dev, s->quirk + 2,             \
-               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db, next_keys, next_count, band_range)
-    if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
+               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db, next_keys, next_count, band_range, band_spec)
+#define FLUID_LAUNCH_FORCE_BAND(EX)                                                                                     \
+    launch_pdl(pdl, k_force_integrate<false, EX, true>, dim3(blocks), dim3(SPH_THREADS), s->stream, p, s->pos_s, s->pred_s, s->vel_s, \
+               s->rho, keys, s->lb_view, s->quirk, s->force_field, s->d_frame_time, goff_dev, s->quirk + 2,             \
+               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db, next_keys, next_count, band_range, band_spec)
+    if (band_range) { if (s->exact_math) FLUID_LAUNCH_FORCE_BAND(true); else FLUID_LAUNCH_FORCE_BAND(false); }
+    else if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
     else { if (s->exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
 #undef FLUID_LAUNCH_FORCE
+#undef FLUID_LAUNCH_FORCE_BAND
     s->launches++;
 }
 
@@ -380,7 +386,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     }
     const uint32_t sblocks = (n + SPH_THREADS - 1) / SPH_THREADS;
     if (!counting) launch_tile_plans(this, p, keys_sorted, pdl);  // counting path: made by k_rank_gather_cells
-    launch_pdl(pdl, k_density, dim3(sblocks), dim3(SPH_THREADS), stream, p, pred_s, keys_sorted, cell_lb, quirk, rho, quirk + 2,
+    launch_pdl(pdl, k_density<false>, dim3(sblocks), dim3(SPH_THREADS), stream, p, pred_s, keys_sorted, cell_lb, quirk, rho, quirk + 2,
                d_frame_time, reinterpret_cast<const TilePlan*>(tile_plans), (const uint32_t*)nullptr);
     launches++;
     mark("density");

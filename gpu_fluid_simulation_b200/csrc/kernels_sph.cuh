@@ -22,6 +22,7 @@
 // (a row boundary inside a long row) falls back to walking the same spans straight from global/L2.
 #pragma once
 #include "common.cuh"
+#include "band_common.cuh"
 
 namespace fluid {
 
@@ -303,6 +304,7 @@ __device__ __forceinline__ float density_walk_staged(const DevParams& p, uint32_
     return density;
 }
 
+template <bool BAND>
 __global__ void __launch_bounds__(SPH_THREADS)
 k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* __restrict__ keys,
           const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk, float* __restrict__ rho,
@@ -315,10 +317,11 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
     pdl_enter();
     // band mode (kernels_band.cuh): the key-ordered arrays hold [ghost rows | owned | ghost rows]; density is computed for
     // the owned particles and one ghost row on each side, a range only the device knows
-    const uint32_t r_begin = band_range ? __ldg(band_range) : p.own_begin;
-    const uint32_t r_end = band_range ? __ldg(band_range + 1) : p.own_begin + p.n;
-    const uint32_t i0 = (band_range ? 0u : p.own_begin) + blockIdx.x * SPH_THREADS;
-    if (i0 + SPH_THREADS <= r_begin || i0 >= r_end) return;  // (whole CTA; never true on a single GPU)
+    // (BAND is a template parameter so that the single-GPU kernel is compiled exactly as it was without band support)
+    const uint32_t r_begin = BAND ? __ldg(band_range) : p.own_begin;
+    const uint32_t r_end = BAND ? __ldg(band_range + 1) : p.own_begin + p.n;
+    const uint32_t i0 = (BAND ? 0u : p.own_begin) + blockIdx.x * SPH_THREADS;
+    if (BAND && (i0 + SPH_THREADS <= r_begin || i0 >= r_end)) return;  // (whole CTA)
     if (threadIdx.x == 0) {
         mbar_init(&s_bar, 1);
         mbar_fence_init();
@@ -328,7 +331,7 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
         stage_from_plan<1>(plans + blockIdx.x, arrays, smem, eb, &s_bar, &s_plan);
     }
     const uint32_t i = i0 + threadIdx.x;
-    const bool valid = i >= r_begin && i < r_end;
+    const bool valid = BAND ? (i >= r_begin && i < r_end) : (i < r_end);
     uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
     float2 me = make_float2(0.f, 0.f);
     uint32_t cy = 0;
@@ -352,20 +355,6 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
         const float dens = fmaxf(fmaxf(d, 1.19209290e-07f), 0.1f);
         rho[i] = dens;
         if (wild_stamp && !(dens <= DIV_DEN_HI)) *wild_stamp = __ldg(frame_time);  // common.cuh tame_component
-    }
-}
-
-// count[cell] += 1 for every valid lane, one atomic per run of equal cells along the lanes (kernels_count.cuh
-// cell_count_add is this function; it lives here because the force pass uses it too)
-__device__ __forceinline__ void atomic_count_run(uint32_t* __restrict__ count, uint32_t cell, bool valid) {
-    const uint32_t lane = lane_id();
-    const uint32_t d = valid ? cell : 0xffffffffu;
-    const uint32_t prev = __shfl_up_sync(0xffffffffu, d, 1);
-    const uint32_t heads = __ballot_sync(0xffffffffu, lane == 0u || d != prev);
-    if (valid && ((heads >> lane) & 1u)) {
-        const uint32_t above = heads & ~((2u << lane) - 1u);  // run heads in the lanes above this one
-        const uint32_t next = above ? (uint32_t)__ffs(above) - 1u : 32u;
-        atomicAdd(count + cell, next - lane);
     }
 }
 
@@ -836,7 +825,7 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
     }
 }
 
-template <bool DEBUG, bool EXACT>
+template <bool DEBUG, bool EXACT, bool BAND>
 __global__ void __launch_bounds__(SPH_THREADS, FLUID_FORCE_MIN_CTAS)
 k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const float2* __restrict__ pred_s,
                   const float2* __restrict__ vel_s, const float* __restrict__ rho, const uint32_t* __restrict__ keys,
@@ -848,7 +837,8 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
                   float2* __restrict__ pos_out, float2* __restrict__ vel_out, float2* __restrict__ dbg_accel,
                   float2* __restrict__ dbg_abs,
                   uint32_t* __restrict__ next_keys /* null: do not speculate */, uint32_t* __restrict__ next_count,
-                  const uint32_t* __restrict__ band_range /* multi-GPU band: {first, end} of the owned particles, on the device; else null */) {
+                  const uint32_t* __restrict__ band_range /* multi-GPU band: {first, end} of the owned particles, on the device; else null */,
+                  const BandSpec* __restrict__ band_spec /* multi-GPU band: run the next tick's key pass (band_common.cuh) into next_keys / next_count; else null */) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP];
     __shared__ __align__(128) float2 s_vel[SPH_CAP];
     __shared__ __align__(128) float s_rho[SPH_CAP];
@@ -857,10 +847,14 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     __shared__ SpanPlan s_plan;
     pdl_enter();
     // band mode: owned particles are [first, end) of arrays that also hold ghost rows on both sides (see k_density)
-    const uint32_t r_begin = band_range ? __ldg(band_range) : p.own_begin;
-    const uint32_t r_end = band_range ? __ldg(band_range + 1) : p.own_begin + p.n;
-    const uint32_t i0 = (band_range ? 0u : p.own_begin) + blockIdx.x * SPH_THREADS;
-    if (i0 + SPH_THREADS <= r_begin || i0 >= r_end) return;  // (whole CTA; never true on a single GPU)
+    // (BAND is a template parameter so that the single-GPU kernel is compiled exactly as it was without band support)
+    const uint32_t r_begin = BAND ? __ldg(band_range) : p.own_begin;
+    const uint32_t r_end = BAND ? __ldg(band_range + 1) : p.own_begin + p.n;
+    const uint32_t i0 = (BAND ? 0u : p.own_begin) + blockIdx.x * SPH_THREADS;
+    if (BAND && (i0 + SPH_THREADS <= r_begin || i0 >= r_end)) {  // (whole CTA)
+        if (band_spec) band_key_pass_done(band_spec->rows, band_spec->out, band_spec->dyn, r_end - r_begin);
+        return;
+    }
     if (threadIdx.x == 0) {
         mbar_init(&s_bar, 1);
         mbar_fence_init();
@@ -870,7 +864,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
         stage_from_plan<3>(plans + blockIdx.x, arrays, smem, eb, &s_bar, &s_plan);
     }
     const uint32_t i = i0 + threadIdx.x;
-    const bool valid = i >= r_begin && i < r_end;
+    const bool valid = BAND ? (i >= r_begin && i < r_end) : (i < r_end);
     uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
     float2 pos = make_float2(0.f, 0.f), pred = pos, vel = pos;
     float dens = 1.0f;
@@ -962,7 +956,15 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     // exactly this position and velocity, so the key and the per-cell count are emitted here — same functions, same
     // bits as k_predict_key_count — and the next tick starts at the cell scan. The host drops the speculation when the
     // next tick's delta differs or the state was replaced (fluid_sim.cu enqueue_tick).
-    if (next_keys) {
+    if (BAND && band_spec) {
+        // a band of the multi-GPU step: the same, plus the copies for the other ranks and the message headers (k_band_key)
+        const float2 q = predict_position(p, make_float2(nx, ny), make_float2(vx, vy));
+        uint32_t row;
+        const uint32_t k = band_key_and_count(p, band_spec->rows, q, rcp_refined(p.h), valid, band_spec->key_lo, next_count, row);
+        if (valid) next_keys[out_i] = k;
+        band_push_copies(band_spec->rows, band_spec->out, band_spec->dyn, valid, row, make_float2(nx, ny), make_float2(vx, vy), goff + out_i);
+        band_key_pass_done(band_spec->rows, band_spec->out, band_spec->dyn, r_end - r_begin);
+    } else if (next_keys) {
         uint32_t k = 0;
         if (valid) {
             const float2 q = predict_position(p, make_float2(nx, ny), make_float2(vx, vy));
