@@ -13,8 +13,8 @@
 //                          The key's row decides everything: still inside the band's extended rows -> counted into the
 //                          band's cell histogram, else the particle leaves (sentinel key, dropped by the sort). A COPY of
 //                          (pos, vel, origin) goes into the outbox of every other rank whose extended rows contain the
-//                          row: as an immigrant where that rank owns the row, as a ghost otherwise. The last CTA writes
-//                          the message headers (record count, row of the migration matrix).
+//                          row: as an immigrant where that rank owns the row, as a ghost otherwise. k_band_headers (one
+//                          warp) then writes the message headers (record count, row of the migration matrix).
 //   2. [exchange]          one grouped NCCL send/recv per tick (fixed-size windows, the counts travel in the header), or
 //                          device copies when the ranks share a process and a device (tests)
 //   3. k_band_recv         appends the received records behind the natives, keys + histogram as in 1; one thread folds the
@@ -60,7 +60,6 @@ k_band_key(const DevParams p, const BandSpec* __restrict__ spec, const float2* _
         const uint32_t org = origin_explicit ? (v ? __ldg(origin_explicit + i) : 0u) : goff_prev + i;
         band_push_copies(rows, spec->out, dyn, v, row, ps, vs, org);
     }
-    band_key_pass_done(rows, spec->out, dyn, n_nat);
 }
 
 // 3. received records -> behind the natives; keys + histogram; one thread resolves the tick's sizes

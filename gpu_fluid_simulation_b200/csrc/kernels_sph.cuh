@@ -851,10 +851,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     const uint32_t r_begin = BAND ? __ldg(band_range) : p.own_begin;
     const uint32_t r_end = BAND ? __ldg(band_range + 1) : p.own_begin + p.n;
     const uint32_t i0 = (BAND ? 0u : p.own_begin) + blockIdx.x * SPH_THREADS;
-    if (BAND && (i0 + SPH_THREADS <= r_begin || i0 >= r_end)) {  // (whole CTA)
-        if (band_spec) band_key_pass_done(band_spec->rows, band_spec->out, band_spec->dyn, r_end - r_begin);
-        return;
-    }
+    if (BAND && (i0 + SPH_THREADS <= r_begin || i0 >= r_end)) return;  // (whole CTA)
     if (threadIdx.x == 0) {
         mbar_init(&s_bar, 1);
         mbar_fence_init();
@@ -957,13 +954,12 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     // bits as k_predict_key_count — and the next tick starts at the cell scan. The host drops the speculation when the
     // next tick's delta differs or the state was replaced (fluid_sim.cu enqueue_tick).
     if (BAND && band_spec) {
-        // a band of the multi-GPU step: the same, plus the copies for the other ranks and the message headers (k_band_key)
+        // a band of the multi-GPU step: the same, plus the copies for the other ranks (k_band_key)
         const float2 q = predict_position(p, make_float2(nx, ny), make_float2(vx, vy));
         uint32_t row;
         const uint32_t k = band_key_and_count(p, band_spec->rows, q, rcp_refined(p.h), valid, band_spec->key_lo, next_count, row);
         if (valid) next_keys[out_i] = k;
         band_push_copies(band_spec->rows, band_spec->out, band_spec->dyn, valid, row, make_float2(nx, ny), make_float2(vx, vy), goff + out_i);
-        band_key_pass_done(band_spec->rows, band_spec->out, band_spec->dyn, r_end - r_begin);
     } else if (next_keys) {
         uint32_t k = 0;
         if (valid) {

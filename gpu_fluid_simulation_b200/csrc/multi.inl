@@ -262,6 +262,8 @@ static int band_enqueue_key(Multi* m, Band* b, const FluidTickSettings& t, DevPa
         s->launches++;
     }
     b->count_dirty = false;
+    launch_pdl(s->pdl, k_band_headers, dim3(1), dim3(32), s->stream, (const BandSpec*)b->spec_dev);
+    s->launches++;
     s->mark("predict+key+hist");
     FLUID_CUDA(cudaGetLastError());
     return FLUID_OK;
@@ -299,7 +301,11 @@ static int band_enqueue_rest(Multi* m, Band* b, const DevParams& p) {
     s->keys_sorted = s->keys_b;
     // the force pass also runs the NEXT tick's key pass (keys into keys_u: the slot pass is done with it; histogram into the
     // count array the next tick will use, cleared by this tick's scan; copies into the outboxes: this tick's exchange has read them)
-    const bool spec = s->speculate && m->world >= 1;
+    const bool spec = s->speculate;
+    if (spec && m->transport == FLUID_TRANSPORT_LOCAL && m->world > 1) {
+        // the epilogue writes this band's outboxes: every destination must have pulled this tick's records out of them
+        for (Band* d : m->bands) if (d != b) FLUID_CUDA(cudaStreamWaitEvent(s->stream, d->ev_copied, 0));
+    }
     launch_force(s, p, tiles, s->pos_a, s->vel_a, pdl, spec ? s->keys_u : nullptr, spec ? count_next : nullptr, &b->dyn->own_begin, &b->dyn->goff,
                  spec ? b->spec_dev : nullptr);
     if (spec) { b->spec_valid = true; b->count_dirty = true; b->spec_delta = s->last_uniform.delta; }
@@ -400,7 +406,7 @@ static int multi_init_common(Multi* m, const FluidSimSettings* s, int world, con
     }
     const uint32_t rows_inner = std::max(1u, m->grid_h - 2u);
     const uint32_t per_row = (uint32_t)std::min<uint64_t>(((uint64_t)s->particle_count + rows_inner - 1) / rows_inner, 1u << 26);
-    m->window_near = (opt && opt->window_near) ? opt->window_near : std::max(16u * per_row, 8192u);
+    m->window_near = (opt && opt->window_near) ? opt->window_near : std::max(8u * per_row, 8192u);
     m->window_far = (opt && opt->window_far) ? opt->window_far : 1024u;
     m->transport = opt ? opt->transport : FLUID_TRANSPORT_AUTO;
     return FLUID_OK;

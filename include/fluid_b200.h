@@ -259,7 +259,7 @@ int fluid_sim_set_particle_count(FluidSim* sim, uint32_t n);
 typedef struct FluidMultiOptions {
     uint32_t row_bounds[FLUID_MULTI_MAX_RANKS + 1]; /* rank r owns grid rows [row_bounds[r], row_bounds[r+1]); all zero: equal bands */
     uint32_t capacity;     /* particles a rank can own; 0: particle_count / ranks * 1.25 + 4096 */
-    uint32_t window_near;  /* records per exchange window between adjacent ranks (2 ghost rows + migrants each way); 0: max(16 x average row, 8192) */
+    uint32_t window_near;  /* records per exchange window between adjacent ranks (2 ghost rows + migrants each way); 0: max(8 x average row, 8192) */
     uint32_t window_far;   /* records per window between non-adjacent ranks (long jumps: the force-field push-out, compute.wgsl:131-136); 0: 1024 */
     int32_t transport;     /* FLUID_TRANSPORT_* */
     uint32_t reserved[4];
