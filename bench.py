@@ -38,6 +38,9 @@ WORKLOADS = {  # name -> (kind, args)
 # algorithmic bytes per particle-step, by pass
 ALGO_BYTES = {"predict+key+hist": 28, "sort": 52, "gather+cells": 52 + 8, "density": 16, "force+integrate": 44}
 ALGO_BYTES_TOTAL = 200
+# bytes the kernels of a phase actually read + write per particle, by sort path
+MOVED_BYTES = {"counting": {"sort": 14, "gather+cells": 49, "density": 8 + 4 + 4 + 24, "force+integrate": 8 + 8 + 8 + 4 + 24 + 16 + 4},
+               "radix": {"predict+key+hist": 20, "sort": 44, "gather+cells": 60, "density": 8 + 4 + 4 + 24, "force+integrate": 8 + 8 + 8 + 4 + 24 + 16 + 4}}
 
 
 def peaks():
@@ -210,6 +213,7 @@ def main():
                     help="key-order path of the single-GPU tick (include/fluid_b200.h FLUID_SORT_*): identical results")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-also", action="store_true", help="skip the short 1M / default-scene / fast-math timings appended to the line")
     ap.add_argument("--no-parity", action="store_true", help="--gpus > 1: skip the NCCL-path-vs-single-GPU parity check before timing")
     ap.add_argument("--e2e-steps", type=int, default=6)
     args = ap.parse_args()
@@ -325,12 +329,41 @@ def main():
                 "between_ticks_ms": None if between_ticks_ms is None else round(between_ticks_ms, 5),
                 "phases_source": "events inside the timed region" if marks_in_region else
                                  "second pass of the same K steps with per-phase events (the timed region runs without them)",
-                "phase_frac_of_peak": {k: round(algo[k] * n / (v * 1e-3) / 1e9 / peak, 4) for k, v in phases if v > 0 and k in algo}}
+                "phase_frac_of_peak": {k: round(algo[k] * n / (v * 1e-3) / 1e9 / peak, 4) for k, v in phases if v > 0 and k in algo},
+                "phase_bytes": {"note": "phase_frac_of_peak charges SURVEY.md 8(d)'s per-particle model (a 3-pass radix sort) to every phase; "
+                                        "the counting path moves far fewer bytes in 'sort' and 'gather+cells', so those model fractions "
+                                        "exceed 1 without any kernel exceeding the HBM peak: moved_frac_of_peak uses the bytes actually moved",
+                                "algorithm": sort_path, "survey_model_bytes_per_particle": {k: algo[k] for k in algo},
+                                "moved_bytes_per_particle": MOVED_BYTES[sort_path],
+                                "moved_frac_of_peak": {k: round(MOVED_BYTES[sort_path][k] * n / (v * 1e-3) / 1e9 / peak, 4)
+                                                       for k, v in phases if v > 0 and k in MOVED_BYTES[sort_path]}}}
     traffic_path = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_path):
         with open(traffic_path) as f:
             tj = json.load(f)
         roofline["traffic"] = tj.get(args.workload, {}).get(roofline["kernel"])  # bytes per launch, ncu (profiles/)
+
+    # ---- the same K steps in FLUID_MATH_FAST (hardware rsqrt / rcp + FMA in the pair terms: <= 1e-5 of sum|terms| from
+    # the exact mode, inside the north star's tolerance; keys, order, tables, densities unchanged) ----------------------
+    also = None
+    if not args.no_also:
+        sim.math_mode = 1
+        sim.tick_n(ts, 3)
+        sim.sync()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sim.enable_timing(True)
+        with torch.cuda.stream(stream):
+            f0.record(stream)
+            sim.tick_n(ts, args.steps)
+            f1.record(stream)
+        sim.sync()
+        fast_ms = f0.elapsed_time(f1) / args.steps
+        roofline["fast_math"] = {"ms_per_step": fast_ms, "value": n / (fast_ms * 1e-3),
+                                 "force_ms": dict(sim.last_timing()).get("force+integrate")}
+        sim.enable_timing(False)
+        sim.math_mode = 1 if args.math == "fast" else 0
+        sim.tick_n(ts, 1)
+        sim.sync()
 
     # ---- end to end through the public API with host buffers -------------------------------------
     e2e = None
@@ -392,9 +425,31 @@ def main():
                                 "note": "state resident (as in the reference); per step: force-field upload + tick + headless "
                                         "960x540 render downloaded to the host"}
 
+    sim.close()
+    # ---- the metric's other sizes (BASELINE.json: "at 1M & 64M particles"), a second or two each --------------------
+    if not args.no_also and args.workload == "64m-u":
+        also = {}
+        for name, wl, warm, steps in (("1m-u", "1m-u", 20, 400), ("1m-d", "1m-d", 20, 200), ("1m-d after 300 ticks", "1m-d", 320, 200),
+                                      ("default (100k, the reference's scene)", "default", 20, 400)):
+            s2, ts2, p2 = make_scene(wl)
+            with fluid.FluidSimulation.new(local_rank, s2) as sim2:
+                if p2 is not None:
+                    sim2.upload_particles(p2)
+                sim2.tick_n(ts2, warm)
+                sim2.sync()
+                st2 = torch.cuda.ExternalStream(sim2.stream, device=local_rank)
+                g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                with torch.cuda.stream(st2):
+                    g0.record(st2)
+                    sim2.tick_n(ts2, steps)
+                    g1.record(st2)
+                sim2.sync()
+                ms2 = g0.elapsed_time(g1) / steps
+                also[name] = {"particles": s2.particle_count, "ms_per_step": round(ms2, 5), "value": s2.particle_count / (ms2 * 1e-3),
+                              "steps": steps, "warmup": warm, "sort_path": "counting" if sim2.last_sort_path == 2 else "radix"}
+
     cpu = None
     if not args.no_cpu_baseline:
-        sim.close()
         cpu = run_cpu(args.workload, 8, warmup=1, budget_s=12.0)
         port = run_cpu(args.workload, 8, warmup=1, budget_s=8.0, kind="port") if cpu["kind"] != "port" else cpu
         cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
@@ -406,7 +461,7 @@ def main():
             "config": {"workload": args.workload, "particles": n, "math": args.math, "sort": args.sort, "sort_path": sort_path,
                        "l2": "inputs larger than L2 (no flush)" if n * 64 > 126e6 * 2 else "state fits L2; steps run back to back as in the real simulation loop (no flush)",
                        "parallelism": "1 GPU"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu}
+            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu, "also": also}
     print(json.dumps(line), flush=True)
 
 

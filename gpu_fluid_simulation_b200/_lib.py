@@ -148,6 +148,7 @@ PROTOTYPES = {
     "fluid_sim_field_from_objects": (_i, [_P, _P, _u32, _P, _P, _P, _P, C.POINTER(C.c_float)]),
     "fluid_sim_field_from_mask": (_i, [_P, _P, _P, _P, C.POINTER(C.c_float)]),
     "fluid_sim_render": (_i, [_P, _P, _u32, _u32, _P, _P, C.POINTER(C.c_float)]),
+    "fluid_sim_render_frame": (_i, [_P, _P, _u32, _u32, _P, _i, _i]),
     "fluid_sim_surface_tension": (_i, [_P, _P]),
     "fluid_mouse_world_pos": (_i, [_P, _P, _P, _P]),
     "fluid_selftest_division": (_i, [_i, _u32, _i, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64),

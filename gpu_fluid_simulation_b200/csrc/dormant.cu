@@ -115,14 +115,19 @@ extern "C" int fluid_sim_surface_tension(FluidSim* h_, float* force_xy_out) {
     q.c_grad = -24.0f / (PI_WGSL * h8);
     q.c_lap = 8.0f / (PI_WGSL * h8);
     q.grid_w = s->grid_w; q.num_cells = s->num_cells; q.n = s->n; q.frame_time = u.frame_time;
-    float2* d_out = nullptr;
-    FLUID_CUDA(cudaMalloc(&d_out, (size_t)s->n * sizeof(float2)));
+    const size_t need = (size_t)s->n * sizeof(float2);
+    if (need > s->diag_bytes) {  // grown on demand, kept
+        FLUID_CUDA(cudaStreamSynchronize(s->stream));
+        if (s->diag_out) cudaFree(s->diag_out);
+        s->diag_out = nullptr; s->diag_bytes = 0;
+        FLUID_CUDA(cudaMalloc(&s->diag_out, need));
+        s->diag_bytes = need;
+    }
+    float2* d_out = reinterpret_cast<float2*>(s->diag_out);
     k_surface_tension<<<(s->n + 127) / 128, 128, 0, s->stream>>>(q, s->pred_s, s->rho, s->keys_view(), s->start_indices, d_out);
     s->launches++;
     cudaMemcpyAsync(force_xy_out, d_out, (size_t)s->n * sizeof(float2), cudaMemcpyDeviceToHost, s->stream);
-    cudaError_t e = cudaStreamSynchronize(s->stream);
-    cudaFree(d_out);
-    FLUID_CUDA(e);
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));
     FLUID_CUDA(cudaGetLastError());
     return FLUID_OK;
 }

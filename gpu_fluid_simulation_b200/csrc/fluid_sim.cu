@@ -84,7 +84,8 @@ int Sim::alloc(uint32_t cap) {
     // free old particle-sized buffers, allocate new; contents are NOT preserved
     void** bufs[] = {(void**)&pos_a, (void**)&vel_a, (void**)&pos_s, (void**)&vel_s, (void**)&pred_s, (void**)&rho,
                      (void**)&keys_u, (void**)&keys_b, (void**)&keys_c, (void**)&idx_a, (void**)&idx_b,
-                     (void**)&sort_scratch, (void**)&aos_stage, (void**)&dbg_accel, (void**)&dbg_abs, (void**)&tile_plans};
+                     (void**)&sort_scratch, (void**)&aos_stage, (void**)&dbg_accel, (void**)&dbg_abs, (void**)&tile_plans,
+                     (void**)&nb_head, (void**)&nb_mask};
     for (void** b : bufs) { if (*b) cudaFree(*b); *b = nullptr; }
     capacity = cap;
     const size_t padded = (size_t)cap + 64;
@@ -103,6 +104,9 @@ int Sim::alloc(uint32_t cap) {
     sort_scratch_words = (size_t)MAX_PASSES * RADIX + RADIX + (size_t)MAX_PASSES * max_tiles * RADIX;
     FLUID_CUDA(cudaMalloc(&sort_scratch, sort_scratch_words * 4));
     FLUID_CUDA(cudaMalloc(&tile_plans, ((size_t)cap / SPH_THREADS + 2) * sizeof(TilePlan)));
+    if (padded >= (1ull << 30)) { set_error("capacity must stay below 2^30 particles"); return FLUID_ERR_INVALID_ARGUMENT; }
+    FLUID_CUDA(cudaMalloc(&nb_head, padded * sizeof(uint4)));
+    FLUID_CUDA(cudaMalloc(&nb_mask, padded * sizeof(uint2)));
     keys_sorted = keys_b;
     return FLUID_OK;
 }
@@ -228,11 +232,13 @@ void launch_force(Sim* s, const DevParams& p, uint32_t blocks, float2* pos_out, 
 #define FLUID_LAUNCH_FORCE(DBG, EX)                                                                                     \
     launch_pdl(pdl, k_force_integrate<DBG, EX, false>, dim3(blocks), dim3(SPH_THREADS), s->stream, p, s->pos_s, s->pred_s, s->vel_s, \
                s->rho, keys, s->lb_view, s->quirk, s->force_field, s->d_frame_time, goff_dev, s->quirk + 2,             \
-               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db, next_keys, next_count, band_range, band_spec)
+               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db, next_keys, next_count, band_range, band_spec,      \
+               (const uint4*)s->nb_head, (const uint2*)s->nb_mask)
 #define FLUID_LAUNCH_FORCE_BAND(EX)                                                                                     \
     launch_pdl(pdl, k_force_integrate<false, EX, true>, dim3(blocks), dim3(SPH_THREADS), s->stream, p, s->pos_s, s->pred_s, s->vel_s, \
                s->rho, keys, s->lb_view, s->quirk, s->force_field, s->d_frame_time, goff_dev, s->quirk + 2,             \
-               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db, next_keys, next_count, band_range, band_spec)
+               reinterpret_cast<const TilePlan*>(s->tile_plans), pos_out, vel_out, da, db, next_keys, next_count, band_range, band_spec,      \
+               (const uint4*)s->nb_head, (const uint2*)s->nb_mask)
     if (band_range) { if (s->exact_math) FLUID_LAUNCH_FORCE_BAND(true); else FLUID_LAUNCH_FORCE_BAND(false); }
     else if (s->debug_force) { if (s->exact_math) FLUID_LAUNCH_FORCE(true, true); else FLUID_LAUNCH_FORCE(true, false); }
     else { if (s->exact_math) FLUID_LAUNCH_FORCE(false, true); else FLUID_LAUNCH_FORCE(false, false); }
@@ -387,7 +393,7 @@ int Sim::enqueue_tick(const FluidTickSettings& t, bool hash_sort_only) {
     const uint32_t sblocks = (n + SPH_THREADS - 1) / SPH_THREADS;
     if (!counting) launch_tile_plans(this, p, keys_sorted, pdl);  // counting path: made by k_rank_gather_cells
     launch_pdl(pdl, k_density<false>, dim3(sblocks), dim3(SPH_THREADS), stream, p, pred_s, keys_sorted, cell_lb, quirk, rho, quirk + 2,
-               d_frame_time, reinterpret_cast<const TilePlan*>(tile_plans), (const uint32_t*)nullptr);
+               d_frame_time, reinterpret_cast<const TilePlan*>(tile_plans), (const uint32_t*)nullptr, nb_head, nb_mask);
     launches++;
     mark("density");
     // the force pass emits the next tick's keys (into keys_c: free on the counting path, and the radix passes of THIS tick are
@@ -542,10 +548,12 @@ void fluid_sim_destroy(FluidSim* h) {
     cudaSetDevice(s->device);
     if (s->stream) cudaStreamSynchronize(s->stream);
     void* bufs[] = {s->pos_a, s->vel_a, s->pos_s, s->vel_s, s->pred_s, s->rho, s->keys_u, s->keys_b, s->keys_c, s->idx_a,
-                    s->idx_b, s->sort_scratch, s->tile_plans, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
+                    s->idx_b, s->sort_scratch, s->tile_plans, s->nb_head, s->nb_mask, s->aos_stage, s->dbg_accel, s->dbg_abs, s->start_indices, s->cell_lb, s->quirk,
                     s->d_frame_time, s->force_field, s->jfa_a, s->jfa_b,
                     s->mask_dev, s->mask_flag, s->objects_dev, s->cell_count_buf[0], s->cell_count_buf[1], s->cell_tile_sum, s->cell_tile_max, s->cell_tile_sq, s->cell_cursor};
     for (void* b : bufs) if (b) cudaFree(b);
+    for (void* b : {s->frame_f32, s->frame_u8, s->diag_out}) if (b) cudaFree(b);
+    for (cudaEvent_t e : {s->ev_frame0, s->ev_frame1}) if (e) cudaEventDestroy(e);
     if (s->cell_max_host) cudaFreeHost((void*)s->cell_max_host);
     if (s->h2d_stream) { cudaStreamSynchronize(s->h2d_stream); cudaStreamDestroy(s->h2d_stream); }
     if (s->d2h_stream) { cudaStreamSynchronize(s->d2h_stream); cudaStreamDestroy(s->d2h_stream); }
@@ -862,38 +870,51 @@ int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
     SIM_OR_FAIL(h);
     NOT_SLAB(s);
     if (capacity <= s->capacity) return FLUID_OK;
-    if (s->aos_in) {  // pipelined-transfer staging is sized by the capacity: drain and drop, re-created on next use
-        FLUID_CUDA(cudaStreamSynchronize(s->h2d_stream));
-        FLUID_CUDA(cudaStreamSynchronize(s->stream));
-        FLUID_CUDA(cudaStreamSynchronize(s->d2h_stream));
-        cudaFree(s->aos_in); cudaFree(s->aos_out);
-        s->aos_in = s->aos_out = nullptr;
-    }
-    // contents are preserved through a host-free device round trip of the live arrays
-    const uint32_t n = s->n;
-    float2 *pa = nullptr, *va = nullptr, *pr = nullptr; float* rh = nullptr; uint32_t* ks = nullptr;
-    FLUID_CUDA(cudaMalloc(&pa, (size_t)n * 8)); FLUID_CUDA(cudaMalloc(&va, (size_t)n * 8)); FLUID_CUDA(cudaMalloc(&pr, (size_t)n * 8));
-    FLUID_CUDA(cudaMalloc(&rh, (size_t)n * 4)); FLUID_CUDA(cudaMalloc(&ks, (size_t)n * 4));
-    FLUID_CUDA(cudaMemcpyAsync(pa, s->pos_a, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
-    FLUID_CUDA(cudaMemcpyAsync(va, s->vel_a, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
-    FLUID_CUDA(cudaMemcpyAsync(pr, s->pred_s, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
-    FLUID_CUDA(cudaMemcpyAsync(rh, s->rho, (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream));
-    FLUID_CUDA(cudaMemcpyAsync(ks, s->keys_sorted, (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream));
     FLUID_CUDA(cudaStreamSynchronize(s->stream));
+    if (s->h2d_stream) { FLUID_CUDA(cudaStreamSynchronize(s->h2d_stream)); FLUID_CUDA(cudaStreamSynchronize(s->d2h_stream)); }
+    // The new arrays are allocated FIRST and the old ones freed only after everything succeeded: a failed cudaMalloc
+    // (out of memory at a large capacity) leaves the handle exactly as it was, live state included.
+    void** members[] = {(void**)&s->pos_a, (void**)&s->vel_a, (void**)&s->pos_s, (void**)&s->vel_s, (void**)&s->pred_s, (void**)&s->rho,
+                        (void**)&s->keys_u, (void**)&s->keys_b, (void**)&s->keys_c, (void**)&s->idx_a, (void**)&s->idx_b,
+                        (void**)&s->sort_scratch, (void**)&s->aos_stage, (void**)&s->dbg_accel, (void**)&s->dbg_abs, (void**)&s->tile_plans,
+                        (void**)&s->nb_head, (void**)&s->nb_mask, (void**)&s->aos_in, (void**)&s->aos_out};
+    constexpr int NM = sizeof(members) / sizeof(members[0]);
+    void* old[NM];
+    for (int k = 0; k < NM; k++) { old[k] = *members[k]; *members[k] = nullptr; }
+    const uint32_t old_capacity = s->capacity, old_max_tiles = s->max_tiles, n = s->n;
+    const size_t old_scratch_words = s->sort_scratch_words;
+    uint32_t* const old_keys_sorted = s->keys_sorted;
+    uint32_t* const old_idx_sorted = s->idx_sorted;
     const bool dbg = s->debug_force;
     int rc = s->alloc(capacity);
-    if (rc != FLUID_OK) return rc;
-    FLUID_CUDA(cudaMemcpyAsync(s->pos_a, pa, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
-    FLUID_CUDA(cudaMemcpyAsync(s->vel_a, va, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
-    FLUID_CUDA(cudaMemcpyAsync(s->pred_s, pr, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream));
-    FLUID_CUDA(cudaMemcpyAsync(s->rho, rh, (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream));
-    FLUID_CUDA(cudaMemcpyAsync(s->keys_sorted, ks, (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream));
-    FLUID_CUDA(cudaStreamSynchronize(s->stream));
-    cudaFree(pa); cudaFree(va); cudaFree(pr); cudaFree(rh); cudaFree(ks);
+    if (rc == FLUID_OK && dbg) {
+        s->debug_force = false;
+        rc = fluid_sim_enable_debug_force(h, 1);
+    }
+    if (rc == FLUID_OK && old_keys_sorted) {
+        cudaError_t e = cudaSuccess;
+        const float2 *o_pos = (const float2*)old[0], *o_vel = (const float2*)old[1], *o_pred = (const float2*)old[4];
+        if (e == cudaSuccess) e = cudaMemcpyAsync(s->pos_a, o_pos, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(s->vel_a, o_vel, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(s->pred_s, o_pred, (size_t)n * 8, cudaMemcpyDeviceToDevice, s->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(s->rho, old[5], (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(s->keys_sorted, old_keys_sorted, (size_t)n * 4, cudaMemcpyDeviceToDevice, s->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "fluid_sim_reserve: copy into the new arrays", __FILE__, __LINE__);
+    }
+    if (rc != FLUID_OK) {
+        // roll back: drop whatever the new allocation produced, put the old arrays back
+        for (int k = 0; k < NM; k++) { if (*members[k]) cudaFree(*members[k]); *members[k] = old[k]; }
+        s->capacity = old_capacity; s->max_tiles = old_max_tiles; s->sort_scratch_words = old_scratch_words;
+        s->keys_sorted = old_keys_sorted; s->idx_sorted = old_idx_sorted; s->debug_force = dbg;
+        cudaGetLastError();
+        return rc;
+    }
+    for (int k = 0; k < NM; k++) if (old[k]) cudaFree(old[k]);
+    s->in_used = s->out_used = false;  // (the pipelined-transfer staging buffers are re-created on next use)
     s->idx_sorted = nullptr;
     s->cell_max_known = false;
     s->spec_valid = false;
-    if (dbg) return fluid_sim_enable_debug_force(h, 1);
     return FLUID_OK;
 }
 int fluid_sim_set_particle_count(FluidSim* h, uint32_t n) {

@@ -245,20 +245,24 @@ __device__ __forceinline__ float density_walk_global(const DevParams& p, const f
 // Tried and dropped (round 1): re-assigning particles to threads by neighbour count to even out the warps of the
 // force pass — with the scan it made the candidate walk diverge (5.7 -> 5.9 ms), with a scanner/evaluator split it
 // needed CTA-wide barriers per round (7.2 ms).
+// The loop also records which candidates it accepted — the same test on the same operands the force pass's candidate scan
+// would repeat (compute.wgsl:202 == funcs.wgsl:74 on identical r2) — as a bit string, first candidate in the HIGHEST
+// position reached (shift left by two per iteration, +2 for A, +1 for B: three integer instructions per two candidates);
+// density_walk_staged turns it into a mask with candidate c at bit c.
 __device__ __forceinline__ void density_span(uint32_t addr, uint32_t end, float px, float py, float h2, float norm, float mass,
-                                             float& density) {
+                                             float& density, uint32_t& hits) {
     asm volatile(
         "{\n"
         ".reg .pred ia, ib, vb, go;\n"
         ".reg .f32 sa, sb, ka, kb;\n"
         ".reg .b64 me, pa, pb, s2, d2, k2, hh, nn, mm;\n"
         ".reg .u32 nx;\n"
-        "setp.lt.u32 go, %1, %2;\n"
+        "setp.lt.u32 go, %1, %3;\n"
         "@!go bra DENS_DONE;\n"
-        "mov.b64 me, {%3, %4};\n"
-        "mov.b64 hh, {%5, %5};\n"
-        "mov.b64 nn, {%6, %6};\n"
-        "mov.b64 mm, {%7, %7};\n"
+        "mov.b64 me, {%4, %5};\n"
+        "mov.b64 hh, {%6, %6};\n"
+        "mov.b64 nn, {%7, %7};\n"
+        "mov.b64 mm, {%8, %8};\n"
         "DENS_LOOP:\n"
         ".pragma \"nounroll\";\n"       // ptxas would re-create the x4 / x2 / x1 remainder structure
         "ld.shared.b64 pa, [%1];\n"
@@ -272,37 +276,56 @@ __device__ __forceinline__ void density_span(uint32_t addr, uint32_t end, float 
         "mov.b64 {sb, kb}, pb;\n"
         "add.rn.f32 sa, sa, ka;\n"
         "add.rn.f32 sb, sb, kb;\n"
-        "setp.lt.u32 vb, nx, %2;\n"
+        "setp.lt.u32 vb, nx, %3;\n"
         "mov.b64 s2, {sa, sb};\n"
         "sub.rn.f32x2 d2, hh, s2;\n"
         "mul.rn.f32x2 k2, nn, d2;\n"    // funcs.wgsl:76: norm * d * d * d, left to right
         "mul.rn.f32x2 k2, k2, d2;\n"
         "mul.rn.f32x2 k2, k2, d2;\n"
         "mul.rn.f32x2 k2, mm, k2;\n"    // funcs.wgsl:189-192: mass * kernel
-        "setp.leu.f32 ia, sa, %5;\n"    // funcs.wgsl:74: r2 > h2 -> 0; NaN falls through, as there
-        "setp.leu.and.f32 ib, sb, %5, vb;\n"
+        "setp.leu.f32 ia, sa, %6;\n"    // funcs.wgsl:74: r2 > h2 -> 0; NaN falls through, as there
+        "setp.leu.and.f32 ib, sb, %6, vb;\n"
         "mov.b64 {ka, kb}, k2;\n"
+        "shl.b32 %2, %2, 2;\n"
         "@ia add.rn.f32 %0, %0, ka;\n"
+        "@ia add.u32 %2, %2, 2;\n"
         "@ib add.rn.f32 %0, %0, kb;\n"
+        "@ib add.u32 %2, %2, 1;\n"
         "add.u32 %1, %1, 16;\n"
-        "setp.lt.u32 go, %1, %2;\n"
+        "setp.lt.u32 go, %1, %3;\n"
         "@go bra DENS_LOOP;\n"
         "DENS_DONE:\n"
         "}\n"
-        : "+f"(density), "+r"(addr)
+        : "+f"(density), "+r"(addr), "+r"(hits)
         : "r"(end), "f"(px), "f"(py), "f"(h2), "f"(norm), "f"(mass));
 }
 
 // staged: the three row spans in visiting order, explicit 32-bit shared addresses
 __device__ __forceinline__ float density_walk_staged(const DevParams& p, uint32_t sp_addr, const int (&base)[3],
-                                                     const uint32_t (&a)[3], const uint32_t (&b)[3], float px, float py) {
+                                                     const uint32_t (&a)[3], const uint32_t (&b)[3], float px, float py,
+                                                     uint32_t (&mask)[3], bool& masks_ok) {
     float density = 0.0f;
+    masks_ok = true;
 #pragma unroll
-    for (int r = 0; r < 3; r++)
+    for (int r = 0; r < 3; r++) {
+        uint32_t hits = 0;
         density_span(sp_addr + (a[r] - (uint32_t)base[r]) * 8u, sp_addr + (b[r] - (uint32_t)base[r]) * 8u, px, py, p.h2,
-                     p.poly6_norm, p.mass, density);
+                     p.poly6_norm, p.mass, density, hits);
+        // the loop took ceil(len / 2) iterations: candidate c sits at bit 2 * iterations - 1 - c
+        const uint32_t len = b[r] - a[r];
+        const uint32_t even = (len + 1u) & ~1u;
+        masks_ok = masks_ok && len <= 32u;
+        mask[r] = len ? (__brev(hits) >> (32u - min(even, 32u))) : 0u;
+    }
     return density;
 }
+
+// What the density pass hands to the force pass per particle (24 B): the starts of its three row spans and, per span, the
+// candidates with !(r2 > h2) as a bit mask — so that the force pass neither walks the key -> cell-table chain again nor
+// repeats the distance test on ~36 candidates to find its ~12 neighbours (compute.wgsl:160-299 walks the 9 cells twice
+// more; here they are walked once, by the density pass). head.x bit 31: masks not usable (a span longer than 32
+// candidates, or a tile that was not staged): the force pass scans as before; bit 30: the tile-plan row group.
+constexpr uint32_t NB_FALLBACK = 0x80000000u, NB_GROUP = 0x40000000u, NB_INDEX = 0x3fffffffu;
 
 template <bool BAND>
 __global__ void __launch_bounds__(SPH_THREADS)
@@ -310,7 +333,8 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
           const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk, float* __restrict__ rho,
           uint32_t* __restrict__ wild_stamp, const uint32_t* __restrict__ frame_time,
           const TilePlan* __restrict__ plans,
-          const uint32_t* __restrict__ band_range /* multi-GPU band: {first, end} of the particles to compute, on the device; tiles count from 0. Else null */) {
+          const uint32_t* __restrict__ band_range /* multi-GPU band: {first, end} of the particles to compute, on the device; tiles count from 0. Else null */,
+          uint4* __restrict__ nb_head, uint2* __restrict__ nb_mask /* per particle: span starts + acceptance masks for the force pass */) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP + 2];  // + pad: the pair loop may load one record past a span
     __shared__ uint64_t s_bar;
     __shared__ SpanPlan s_plan;
@@ -342,16 +366,22 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
     __syncthreads();
     const int staged = s_plan.staged;
     float d;
+    uint32_t mask[3] = {0, 0, 0};
+    bool masks_ok = false;
     if (staged) {
         mbar_wait(&s_bar, 0);
         int base[3];
         thread_bases(s_plan, valid ? cy : s_plan.row_first, base);
-        d = density_walk_staged(p, smem_u32_pinned(s_pred), base, a, b, me.x, me.y);
+        d = density_walk_staged(p, smem_u32_pinned(s_pred), base, a, b, me.x, me.y, mask, masks_ok);
     } else {
         d = density_walk_global(p, pred_s, a, b, me.x, me.y);
     }
     // funcs.wgsl:202 max(density, EPSILON); compute.wgsl:70 max(.., 0.1)
     if (valid) {
+        uint32_t g = cy - s_plan.row_first;
+        if (g >= (uint32_t)SPH_MAX_ROWS) g = 0;
+        nb_head[i] = make_uint4((a[0] & NB_INDEX) | (masks_ok ? 0u : NB_FALLBACK) | (g ? NB_GROUP : 0u), a[1], a[2], mask[0]);
+        nb_mask[i] = make_uint2(mask[1], mask[2]);
         const float dens = fmaxf(fmaxf(d, 1.19209290e-07f), 0.1f);
         rho[i] = dens;
         if (wild_stamp && !(dens <= DIV_DEN_HI)) *wild_stamp = __ldg(frame_time);  // common.cuh tame_component
@@ -825,6 +855,55 @@ __device__ __forceinline__ void force_walk_staged(const DevParams& p, uint32_t s
     }
 }
 
+// Staged walk over the neighbours the density pass has already found (nb_head / nb_mask, see k_density): the set bits of the
+// three row masks, in ascending order = the reference's visiting order, two per iteration through force_pair2. No candidate
+// scan, no accepted list, no key -> cell-table look-ups: ~8 integer instructions per neighbour instead of ~31 per neighbour
+// for scanning three candidates to find it. The particle itself (accepted by the density pass, skipped here by index,
+// compute.wgsl:195) lies in its own row's span.
+template <bool DEBUG, bool EXACT>
+__device__ __forceinline__ void force_walk_masked(const DevParams& p, uint32_t sp_addr, uint32_t sv_addr, uint32_t sr_addr,
+                                                  const int (&base)[3], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t m0,
+                                                  uint32_t m1, uint32_t m2, uint32_t self, float px, float py, float vx, float vy,
+                                                  float pressure, bool tame, uint32_t& rand_seed, ForceAcc& acc) {
+    const PairConsts pc = make_pair_consts(p);
+    if (self - a1 < 32u) m1 &= ~(1u << (self - a1));  // (self < a1 wraps: the stale-entry quirk moved the span start past it)
+    const uint32_t addr1 = sp_addr + (a1 - (uint32_t)base[1]) * 8u, addr2 = sp_addr + (a2 - (uint32_t)base[2]) * 8u;
+    const uint32_t vel_delta = sv_addr - sp_addr, rho_base = sr_addr - (sp_addr >> 1);
+    const uint32_t iters = ((uint32_t)(__popc(m0) + __popc(m1) + __popc(m2)) + 1u) >> 1;
+    const uint32_t max_iters = __reduce_max_sync(0xffffffffu, iters);
+    uint32_t m = m0, cur = sp_addr + (a0 - (uint32_t)base[0]) * 8u;
+    int r = 0;
+    auto pop = [&](uint32_t& e) -> bool {
+        while (m == 0u) {
+            if (r == 2) return false;
+            r++;
+            m = r == 1 ? m1 : m2;
+            cur = r == 1 ? addr1 : addr2;
+        }
+        const uint32_t bit = (uint32_t)__ffs((int)m) - 1u;
+        m &= m - 1u;
+        e = cur + bit * 8u;
+        return true;
+    };
+    for (uint32_t it = 0; it < max_iters; it++) {
+        if (it < iters) {
+            uint32_t eA = 0, eB = 0;
+            pop(eA);
+            const bool hasB = pop(eB);
+            if (!hasB) eB = eA;
+            const float2 qA = lds_f2(eA), qB = lds_f2(eB);
+            const float2 nvA = lds_f2(eA + vel_delta), nvB = lds_f2(eB + vel_delta);
+            const float ndA = lds_f((eA >> 1) + rho_base), ndB = lds_f((eB >> 1) + rho_base);
+            if (EXACT)
+                force_pair2<DEBUG>(p, pc, fsub(qA.x, px), fsub(qA.y, py), fsub(qB.x, px), fsub(qB.y, py), nvA, nvB, ndA, ndB,
+                                   hasB, tame, vx, vy, pressure, rand_seed, acc);
+            else
+                force_pair2_fast<DEBUG>(p, pc, fsub(qA.x, px), fsub(qA.y, py), fsub(qB.x, px), fsub(qB.y, py), nvA, nvB, ndA, ndB,
+                                        hasB, vx, vy, pressure, rand_seed, acc);
+        }
+    }
+}
+
 template <bool DEBUG, bool EXACT, bool BAND>
 __global__ void __launch_bounds__(SPH_THREADS, FLUID_FORCE_MIN_CTAS)
 k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const float2* __restrict__ pred_s,
@@ -838,7 +917,8 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
                   float2* __restrict__ dbg_abs,
                   uint32_t* __restrict__ next_keys /* null: do not speculate */, uint32_t* __restrict__ next_count,
                   const uint32_t* __restrict__ band_range /* multi-GPU band: {first, end} of the owned particles, on the device; else null */,
-                  const BandSpec* __restrict__ band_spec /* multi-GPU band: run the next tick's key pass (band_common.cuh) into next_keys / next_count; else null */) {
+                  const BandSpec* __restrict__ band_spec /* multi-GPU band: run the next tick's key pass (band_common.cuh) into next_keys / next_count; else null */,
+                  const uint4* __restrict__ nb_head, const uint2* __restrict__ nb_mask /* from k_density: span starts + acceptance masks */) {
     __shared__ __align__(128) float2 s_pred[SPH_CAP];
     __shared__ __align__(128) float2 s_vel[SPH_CAP];
     __shared__ __align__(128) float s_rho[SPH_CAP];
@@ -862,12 +942,13 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     }
     const uint32_t i = i0 + threadIdx.x;
     const bool valid = BAND ? (i >= r_begin && i < r_end) : (i < r_end);
-    uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
     float2 pos = make_float2(0.f, 0.f), pred = pos, vel = pos;
     float dens = 1.0f;
-    uint32_t cy = 0;
+    uint4 nh = make_uint4(0u, 0u, 0u, 0u);
+    uint2 nm = make_uint2(0u, 0u);
     if (valid) {
-        cy = thread_spans(p, __ldg(keys + i), lb, __ldg(quirk), __ldg(quirk + 1), a, b);
+        nh = __ldg(nb_head + i);
+        nm = __ldg(nb_mask + i);
         pos = __ldg(pos_s + i);
         pred = __ldg(pred_s + i);
         vel = __ldg(vel_s + i);
@@ -881,14 +962,29 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     const float pressure = fmul(p.pressure_constant, fsub(dens, p.rest_density));
     ForceAcc acc = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     __syncthreads();
-    if (s_plan.staged) {
+    const bool staged = s_plan.staged != 0;
+    // the density pass's masks serve a warp unless one of its particles has a span longer than 32 candidates
+    if (staged && !__any_sync(0xffffffffu, valid && (nh.x & NB_FALLBACK))) {
         mbar_wait(&s_bar, 0);
         int base[3];
-        thread_bases(s_plan, valid ? cy : s_plan.row_first, base);
-        force_walk_staged<DEBUG, EXACT>(p, smem_u32_pinned(s_pred), smem_u32_pinned(s_vel), smem_u32_pinned(s_rho), smem_u32_pinned(s_list + threadIdx.x),
-                                        base, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, tame, rand_seed, acc);
+        const uint32_t g = (nh.x & NB_GROUP) ? 1u : 0u;
+#pragma unroll
+        for (int r = 0; r < 3; r++) base[r] = s_plan.base[g * 3 + r];
+        force_walk_masked<DEBUG, EXACT>(p, smem_u32_pinned(s_pred), smem_u32_pinned(s_vel), smem_u32_pinned(s_rho), base, nh.x & NB_INDEX, nh.y,
+                                        nh.z, nh.w, nm.x, nm.y, i, pred.x, pred.y, vel.x, vel.y, pressure, tame, rand_seed, acc);
     } else {
-        force_walk_global<DEBUG, EXACT>(p, pred_s, vel_s, rho, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
+        uint32_t a[3] = {0, 0, 0}, b[3] = {0, 0, 0};
+        uint32_t cy = 0;
+        if (valid) cy = thread_spans(p, __ldg(keys + i), lb, __ldg(quirk), __ldg(quirk + 1), a, b);
+        if (staged) {
+            mbar_wait(&s_bar, 0);
+            int base[3];
+            thread_bases(s_plan, valid ? cy : s_plan.row_first, base);
+            force_walk_staged<DEBUG, EXACT>(p, smem_u32_pinned(s_pred), smem_u32_pinned(s_vel), smem_u32_pinned(s_rho), smem_u32_pinned(s_list + threadIdx.x),
+                                            base, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, tame, rand_seed, acc);
+        } else {
+            force_walk_global<DEBUG, EXACT>(p, pred_s, vel_s, rho, a, b, i, pred.x, pred.y, vel.x, vel.y, pressure, rand_seed, acc);
+        }
     }
     float nx = 0.0f, ny = 0.0f, vx = 0.0f, vy = 0.0f;
     if (valid) {

@@ -295,7 +295,7 @@ static int band_enqueue_rest(Multi* m, Band* b, const DevParams& p) {
     s->mark("gather+cells");
     launch_pdl(pdl, k_density<true>, dim3(tiles), dim3(SPH_THREADS), s->stream, p, (const float2*)s->pred_s, (const uint32_t*)s->keys_b, (const uint32_t*)s->lb_view,
                (const uint32_t*)s->quirk, s->rho, s->quirk + 2, (const uint32_t*)s->d_frame_time, reinterpret_cast<const TilePlan*>(s->tile_plans),
-               (const uint32_t*)&b->dyn->dens_begin);
+               (const uint32_t*)&b->dyn->dens_begin, s->nb_head, s->nb_mask);
     s->launches += 6;
     s->mark("density");
     s->keys_sorted = s->keys_b;

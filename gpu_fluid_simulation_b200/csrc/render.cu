@@ -28,7 +28,12 @@ struct RenderParams {
     float m00, m01, m03, m10, m11, m13, m30, m31, m33;  // m<c><r> of the column-major inv_proj
     float half_bx, half_by, h, half_r2, log_norm;
     uint32_t grid_w, num_cells, n, w, h_px;
+    int srgb;  // encode the UNORM8 image as an *Srgb surface would on store
 };
+// linear -> sRGB transfer function (IEC 61966-2-1), what a Bgra8UnormSrgb / Rgba8UnormSrgb render target applies
+__device__ __forceinline__ float linear_to_srgb(float c) {
+    return c <= 0.0031308f ? 12.92f * c : 1.055f * powf(c, 1.0f / 2.4f) - 0.055f;
+}
 
 __global__ void __launch_bounds__(256)
 k_render_fluid(const RenderParams q, const float2* __restrict__ pred, const float2* __restrict__ vel,
@@ -78,7 +83,8 @@ k_render_fluid(const RenderParams q, const float2* __restrict__ pred, const floa
     if (out) out[o] = make_float4(r, g, b, a);
     if (out_rgba8) {
         // ALPHA_BLENDING over (0,0,0,1): rgb = src.rgb * src.a, a = 1; UNORM8 store (clamp, round to nearest)
-        const float br = clampf(r * a, 0.0f, 1.0f), bg = clampf(g * a, 0.0f, 1.0f), bb = clampf(b * a, 0.0f, 1.0f);
+        float br = clampf(r * a, 0.0f, 1.0f), bg = clampf(g * a, 0.0f, 1.0f), bb = clampf(b * a, 0.0f, 1.0f);
+        if (q.srgb) { br = linear_to_srgb(br); bg = linear_to_srgb(bg); bb = linear_to_srgb(bb); }
         out_rgba8[o] = make_uchar4((unsigned char)__float2uint_rn(br * 255.0f), (unsigned char)__float2uint_rn(bg * 255.0f),
                                    (unsigned char)__float2uint_rn(bb * 255.0f), 255);
     }
@@ -88,46 +94,56 @@ k_render_fluid(const RenderParams q, const float2* __restrict__ pred, const floa
 
 using namespace fluid;
 
-extern "C" int fluid_sim_render(FluidSim* h_, const float inv_proj[16], uint32_t w, uint32_t h, float* rgba_f32_out,
-                                uint8_t* rgba8_out, float* ms_out) {
+static int render_common(FluidSim* h_, const float inv_proj[16], uint32_t w, uint32_t h, float* rgba_f32_out, uint8_t* rgba8_out,
+                         float* ms_out, int srgb, bool sync) {
     if (!h_ || !inv_proj || (!rgba_f32_out && !rgba8_out)) { set_error("fluid_sim_render: null argument"); return FLUID_ERR_INVALID_ARGUMENT; }
     if (w == 0 || h == 0 || w > 16384 || h > 16384) { set_error("fluid_sim_render: bad image size"); return FLUID_ERR_INVALID_ARGUMENT; }
     Sim* s = reinterpret_cast<Sim*>(h_);
     if (s->band) { set_error("fluid_sim_render: not available on a band of a FluidMulti (gather the bands first)"); return FLUID_ERR_UNSUPPORTED; }
     FLUID_CUDA(cudaSetDevice(s->device));
     const size_t npx = (size_t)w * h;
-    float4* d_f = nullptr;
-    uchar4* d_8 = nullptr;
-    if (rgba_f32_out) FLUID_CUDA(cudaMalloc(&d_f, npx * sizeof(float4)));
-    if (rgba8_out) FLUID_CUDA(cudaMalloc(&d_8, npx * sizeof(uchar4)));
-    const FluidSimUniform& u = s->last_uniform;  // the uniform of the last tick (sqr_radius, bounds, grid)
+    if (npx > s->frame_px) {  // grown on demand, kept for the following frames
+        FLUID_CUDA(cudaStreamSynchronize(s->stream));
+        if (s->frame_f32) cudaFree(s->frame_f32);
+        if (s->frame_u8) cudaFree(s->frame_u8);
+        s->frame_f32 = s->frame_u8 = nullptr; s->frame_px = 0;
+        FLUID_CUDA(cudaMalloc(&s->frame_f32, npx * sizeof(float4)));
+        FLUID_CUDA(cudaMalloc(&s->frame_u8, npx * sizeof(uchar4)));
+        s->frame_px = npx;
+    }
+    float4* d_f = rgba_f32_out ? reinterpret_cast<float4*>(s->frame_f32) : nullptr;
+    uchar4* d_8 = rgba8_out ? reinterpret_cast<uchar4*>(s->frame_u8) : nullptr;
     RenderParams q;
     const float* m = inv_proj;
     q.m00 = m[0]; q.m01 = m[1]; q.m03 = m[3]; q.m10 = m[4]; q.m11 = m[5]; q.m13 = m[7]; q.m30 = m[12]; q.m31 = m[13]; q.m33 = m[15];
     q.half_bx = s->settings.size[0] * 0.5f; q.half_by = s->settings.size[1] * 0.5f;
     q.h = s->settings.smoothing_radius;
     q.half_r2 = (s->settings.smoothing_radius * s->settings.smoothing_radius) / 2.0f;
-    (void)u;
     q.log_norm = logf(1.0f + 5.0f);
     q.grid_w = s->grid_w; q.num_cells = s->num_cells; q.n = s->n; q.w = w; q.h_px = h;
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    if (ms_out) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, s->stream); }
+    q.srgb = srgb ? 1 : 0;
+    if (ms_out) {
+        if (!s->ev_frame0) { FLUID_CUDA(cudaEventCreate(&s->ev_frame0)); FLUID_CUDA(cudaEventCreate(&s->ev_frame1)); }
+        cudaEventRecord(s->ev_frame0, s->stream);
+    }
     dim3 grid((w + 15) / 16, (h + 15) / 16);
     k_render_fluid<<<grid, 256, 0, s->stream>>>(q, s->pred_s, s->vel_a, s->keys_view(), s->start_indices, d_f, d_8);
     s->launches++;
-    if (ms_out) cudaEventRecord(e1, s->stream);
+    if (ms_out) cudaEventRecord(s->ev_frame1, s->stream);
     if (rgba_f32_out) cudaMemcpyAsync(rgba_f32_out, d_f, npx * sizeof(float4), cudaMemcpyDeviceToHost, s->stream);
     if (rgba8_out) cudaMemcpyAsync(rgba8_out, d_8, npx * sizeof(uchar4), cudaMemcpyDeviceToHost, s->stream);
-    cudaError_t e = cudaStreamSynchronize(s->stream);
-    if (d_f) cudaFree(d_f);
-    if (d_8) cudaFree(d_8);
-    if (ms_out) {
-        float ms = 0.f;
-        if (e == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
-        *ms_out = ms;
-        cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (sync || ms_out) {
+        FLUID_CUDA(cudaStreamSynchronize(s->stream));
+        if (ms_out) { float ms = 0.f; cudaEventElapsedTime(&ms, s->ev_frame0, s->ev_frame1); *ms_out = ms; }
     }
-    FLUID_CUDA(e);
     FLUID_CUDA(cudaGetLastError());
     return FLUID_OK;
+}
+
+extern "C" int fluid_sim_render(FluidSim* h_, const float inv_proj[16], uint32_t w, uint32_t h, float* rgba_f32_out,
+                                uint8_t* rgba8_out, float* ms_out) {
+    return render_common(h_, inv_proj, w, h, rgba_f32_out, rgba8_out, ms_out, 0, true);
+}
+extern "C" int fluid_sim_render_frame(FluidSim* h_, const float inv_proj[16], uint32_t w, uint32_t h, uint8_t* rgba8_out, int srgb, int wait) {
+    return render_common(h_, inv_proj, w, h, nullptr, rgba8_out, nullptr, srgb, wait != 0);
 }

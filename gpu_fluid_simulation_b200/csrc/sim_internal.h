@@ -32,6 +32,8 @@ struct Sim {
     uint32_t *idx_a = nullptr, *idx_b = nullptr;
     uint32_t *keys_sorted = nullptr, *idx_sorted = nullptr;            // aliases into the above
     uint32_t* sort_scratch = nullptr;
+    uint4* nb_head = nullptr;           // per sorted particle, density pass -> force pass: starts of its three row spans + flags + first mask
+    uint2* nb_mask = nullptr;           // ... and the other two acceptance masks (kernels_sph.cuh NB_*)
     void* tile_plans = nullptr;         // TilePlan per tile of SPH_THREADS sorted particles (kernels_sph.cuh), 64 B each
     size_t sort_scratch_words = 0;
     uint32_t max_tiles = 0;
@@ -80,6 +82,11 @@ struct Sim {
     uint32_t sorted_off = 0;   // index of the first owned particle in pos_s / pred_s / vel_s / rho / sorted keys (band: set by a download)
     uint32_t* lb_view = nullptr;  // the lower-bound table as the neighbour passes index it (by global cell id): cell_lb, or a band's table shifted by its first cell
 
+    // output buffers of the per-frame consumers (render.cu, dormant.cu), grown on demand and kept: a cudaMalloc / cudaFree
+    // pair per frame synchronises the whole device
+    void* frame_f32 = nullptr; void* frame_u8 = nullptr; size_t frame_px = 0;
+    void* diag_out = nullptr; size_t diag_bytes = 0;
+    cudaEvent_t ev_frame0 = nullptr, ev_frame1 = nullptr;
     uint32_t *jfa_a = nullptr, *jfa_b = nullptr;  // packed seed ping-pong for fluid_sim_jfa_from_particles
     size_t jfa_pixels = 0;
     uint8_t* mask_dev = nullptr;                  // obstacle mask at texture size (field.inl)

@@ -371,6 +371,12 @@ int fluid_sim_field_from_mask(FluidSim* sim, const uint8_t* mask, uint32_t* seed
  * (src/renderer.rs:178, :437) as UNORM8 (w*h*4 bytes). Row 0 = top of the framebuffer. */
 int fluid_sim_render(FluidSim* sim, const float inv_proj[16], uint32_t w, uint32_t h, float* rgba_f32_out,
                      uint8_t* rgba8_out, float* ms_out);
+/* The per-frame form: only the blended UNORM8 image, into rgba8_out (pinned memory for an asynchronous copy).
+ * srgb != 0 encodes the colour channels with the sRGB transfer function, as the *Srgb surface format the reference
+ * prefers does on store (src/renderer.rs:137-140: `find(|f| f.is_srgb())`) — those are the bytes the reference's window
+ * shows; srgb == 0 (and fluid_sim_render) store the linear values. wait == 0 only enqueues the frame and its copy on
+ * the sim's stream (complete after fluid_sim_sync). The device images are kept between frames. */
+int fluid_sim_render_frame(FluidSim* sim, const float inv_proj[16], uint32_t w, uint32_t h, uint8_t* rgba8_out, int srgb, int wait);
 
 /* ---- dormant physics --------------------------------------------------------
  * calculate_surface_tension (compute.wgsl:300-498; poly6_kernel_gradient / _laplacian funcs.wgsl:81-98) evaluated

@@ -82,6 +82,26 @@ def test_config4_jfa_4096_from_particles(fluid, oracle, size, n_side):
         assert np.array_equal(fld, oracle.jfa_to_force_field(ref))
 
 
+@pytest.mark.parametrize("scene", ["4m-d", "4m-u"])
+def test_config4_jfa_8192_from_4m_particles(fluid, oracle, scene):
+    """BASELINE.json config 4 as stated: the 8192^2 field (13 passes, shaders/jump_flood.wgsl:17-58) from 4M particles —
+    the long-range field of the 4M dam break and the dense seeds of the 4M uniform box — seed map and derived field
+    exactly equal to the oracle's (a few seconds of CPU per scene)."""
+    s, ts, p = scenes.dam_break(1000, 4000) if scene == "4m-d" else scenes.uniform_box(2000)
+    assert p.shape[0] == 4_000_000
+    size = 8192
+    ref_seeds = oracle.jfa_seed_from_particles(p, s.size, size, size)
+    ref = oracle.jfa_run(ref_seeds)
+    with fluid.FluidSimulation.new(0, s) as sim:
+        sim.upload_particles(p)
+        seeds, fld, ms = sim.jfa_from_particles(size, size)
+    assert np.array_equal(seeds, ref), f"{int((seeds != ref).any(axis=2).sum())} pixels of the 8192^2 seed map differ"
+    assert np.array_equal(fld, oracle.jfa_to_force_field(ref))
+    # the host-buffer entry point on the same seeds (the reference-format rg32uint image in, rg32uint out)
+    assert np.array_equal(fluid.jfa.jfa_run(ref_seeds), ref)
+    assert ms > 0
+
+
 def test_non_canonical_seed_images_take_the_general_path(fluid, oracle):
     """caller-supplied seed values the shader would skip as neighbours (coordinate > width) but that are not the
     INVALID marker: the fast kernels' no-skip argument does not hold, the library must detect them while packing and
