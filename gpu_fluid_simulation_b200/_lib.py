@@ -128,6 +128,9 @@ PROTOTYPES = {
     "fluid_multi_download_particles": (_i, [_P, _P]),
     "fluid_multi_upload_band": (_i, [_P, _P, _u32, _P]),
     "fluid_multi_download_band": (_i, [_P, _i, _P, _u32, C.POINTER(_u32), C.POINTER(_u32)]),
+    "fluid_multi_upload_band_async": (_i, [_P, _P, _u32]),
+    "fluid_multi_download_band_async": (_i, [_P, _P, _u32, _P]),
+    "fluid_multi_sync_transfers": (_i, [_P]),
     "fluid_multi_particle_counts": (_i, [_P, _P]),
     "fluid_multi_download_start_indices": (_i, [_P, _P]),
     "fluid_multi_upload_start_indices": (_i, [_P, _P]),

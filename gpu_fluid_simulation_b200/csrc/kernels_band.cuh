@@ -225,6 +225,34 @@ k_band_rank_gather(const DevParams p, const BandRows rows, uint32_t key_lo, uint
     }
 }
 
+// ---- pipelined host transfers of a band (fluid_multi_upload_band_async / _download_band_async) -------------------------
+__global__ void k_band_set_word(uint32_t* __restrict__ w, uint32_t v) { *w = v; }
+// after an upload whose sizes were all-gathered on the device: the counters band_set_counts writes from the host
+__global__ void k_band_counts_from_gathered(BandDyn* __restrict__ dyn, const uint32_t* __restrict__ gathered, int rank, int world,
+                                            uint32_t n_total) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    uint32_t goff = 0, total = 0;
+    for (int r = 0; r < world; r++) { const uint32_t n = gathered[r]; dyn->n_all[r] = n; total += n; if (r < rank) goff += n; }
+    dyn->own_begin = 0; dyn->own_end = gathered[rank];
+    dyn->dens_begin = 0; dyn->dens_end = gathered[rank];
+    dyn->goff = goff; dyn->goff_prev = goff;
+    for (int r = 0; r < BAND_MAX_RANKS; r++) { dyn->out_count[r] = 0; dyn->e_row[r] = 0; dyn->e_sent[r] = 0; }
+    if (total != n_total) dyn->error |= BAND_ERR_COUNT;
+}
+// the band's first min(cap, size) particles in key order -> AoS; info = {size, global offset}
+__global__ void k_band_soa_to_aos(FluidParticle* __restrict__ aos, uint32_t cap, const BandDyn* __restrict__ dyn,
+                                  const float2* __restrict__ pos, const float2* __restrict__ pred_s, const float2* __restrict__ vel,
+                                  const float* __restrict__ rho_s, const uint32_t* __restrict__ keys_s, uint32_t* __restrict__ info) {
+    const uint32_t ob = dyn->own_begin, n = dyn->own_end - dyn->own_begin;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { info[0] = n; info[1] = dyn->goff; }
+    if (i >= min(n, cap)) return;
+    const float2 a = pos[i], b = pred_s[ob + i], c = vel[i];
+    float4* dst = reinterpret_cast<float4*>(aos + i);
+    dst[0] = make_float4(a.x, a.y, b.x, b.y);
+    dst[1] = make_float4(c.x, c.y, rho_s[ob + i], __uint_as_float(keys_s[ob + i]));
+}
+
 // LOCAL transport (ranks of one process on one device, or peer-accessible devices): a whole window, header first
 __global__ void k_band_copy_box(const uint4* __restrict__ src, uint4* __restrict__ dst, uint32_t cap) {
     const uint32_t cnt = min(reinterpret_cast<const uint32_t*>(src)[0], cap);

@@ -166,7 +166,7 @@ static int band_create(Multi* m, int rank, int device, uint32_t capacity, Band**
     FLUID_CUDA(cudaMalloc(&b->origin, ((size_t)b->state_cap + 64) * 4));
     FLUID_CUDA(cudaMalloc(&b->dyn, sizeof(BandDyn)));
     FLUID_CUDA(cudaMemsetAsync(b->dyn, 0, sizeof(BandDyn), s->stream));
-    FLUID_CUDA(cudaMalloc(&b->scratch_word, 64));
+    FLUID_CUDA(cudaMalloc(&b->scratch_word, 128));  // [0] this band's size, [4..12) the gathered sizes, [12..14) download info
     size_t bytes = 0;
     for (int r = 0; r < m->world; r++) if (r != rank) bytes += 2 * ((band_box_bytes(b->out.cap[r]) + 255) & ~(size_t)255);
     if (bytes) {
@@ -793,6 +793,77 @@ void* fluid_multi_stream(FluidMulti* h, int local_band) {
     Multi* m = reinterpret_cast<Multi*>(h);
     if (local_band < 0 || local_band >= (int)m->bands.size()) return nullptr;
     return (void*)m->bands[local_band]->sim->stream;
+}
+
+// ---- pipelined host transfers of a band: SURVEY.md §8(b) state exposure, full duplex (as fluid_sim_*_particles_async) ----
+// One-rank-per-process handles (or world == 1). Nothing is read back by the host: the band sizes are all-gathered on
+// the device. upload: COLLECTIVE; the ranks' subsets concatenated in rank order are the global array (origins implicit).
+int fluid_multi_upload_band_async(FluidMulti* h, const FluidParticle* src, uint32_t n) {
+    MULTI_OR_FAIL(h);
+    if (m->single_process && m->world > 1) { set_error("fluid_multi_upload_band_async: one-rank-per-process handles only"); return FLUID_ERR_INVALID_ARGUMENT; }
+    if (!src && n) { set_error("fluid_multi_upload_band_async: null source"); return FLUID_ERR_INVALID_ARGUMENT; }
+    Band* b = m->bands[0];
+    Sim* s = b->sim;
+    FLUID_CUDA(cudaSetDevice(s->device));
+    if (n > b->capacity) { set_error("fluid_multi_upload_band_async: more particles than the band's capacity"); return FLUID_ERR_INVALID_ARGUMENT; }
+    int rc = ensure_pipeline(s);
+    if (rc != FLUID_OK) return rc;
+    if (s->in_used) FLUID_CUDA(cudaStreamWaitEvent(s->h2d_stream, s->ev_in_free, 0));
+    if (n) FLUID_CUDA(cudaMemcpyAsync(s->aos_in, src, (size_t)n * sizeof(FluidParticle), cudaMemcpyHostToDevice, s->h2d_stream));
+    FLUID_CUDA(cudaEventRecord(s->ev_h2d_done, s->h2d_stream));
+    FLUID_CUDA(cudaStreamWaitEvent(s->stream, s->ev_h2d_done, 0));
+    s->n = n;
+    s->sorted_off = 0;
+    s->keys_sorted = s->keys_b;
+    if (n) {
+        k_aos_to_soa<<<(n + 255) / 256, 256, 0, s->stream>>>(s->aos_in, n, s->pos_a, s->pred_s, s->vel_a, s->rho, s->keys_b);
+        s->launches++;
+    }
+    FLUID_CUDA(cudaEventRecord(s->ev_in_free, s->stream));
+    s->in_used = true;
+    uint32_t* gathered = b->scratch_word + 4;
+    k_band_set_word<<<1, 1, 0, s->stream>>>(m->world > 1 ? b->scratch_word : gathered + b->rows.rank, n);
+    if (m->world > 1) FLUID_NCCL(g_nccl.AllGather(b->scratch_word, gathered, 1, ncclUint32, b->comm, s->stream));
+    k_band_counts_from_gathered<<<1, 32, 0, s->stream>>>(b->dyn, gathered, b->rows.rank, m->world, m->n_total);
+    s->launches += 2;
+    b->explicit_origins = false;
+    if (b->spec_valid) b->count_dirty = true;
+    b->spec_valid = false;
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+// download: the band's first `cap` particles in key order into dst, {size, global offset} into info[2]; dst and info
+// should be pinned; both are valid after fluid_multi_sync_transfers (size > cap: the tail was not copied).
+int fluid_multi_download_band_async(FluidMulti* h, FluidParticle* dst, uint32_t cap, uint32_t* info) {
+    MULTI_OR_FAIL(h);
+    if (m->single_process && m->world > 1) { set_error("fluid_multi_download_band_async: one-rank-per-process handles only"); return FLUID_ERR_INVALID_ARGUMENT; }
+    if (!dst || !info) { set_error("fluid_multi_download_band_async: null destination"); return FLUID_ERR_INVALID_ARGUMENT; }
+    Band* b = m->bands[0];
+    Sim* s = b->sim;
+    FLUID_CUDA(cudaSetDevice(s->device));
+    cap = std::min(cap, b->capacity);
+    int rc = ensure_pipeline(s);
+    if (rc != FLUID_OK) return rc;
+    if (s->out_used) FLUID_CUDA(cudaStreamWaitEvent(s->stream, s->ev_d2h_done, 0));
+    uint32_t* info_dev = b->scratch_word + 12;
+    k_band_soa_to_aos<<<(std::max(cap, 1u) + 255) / 256, 256, 0, s->stream>>>(s->aos_out, cap, b->dyn, s->pos_a, s->pred_s, s->vel_a, s->rho, s->keys_b, info_dev);
+    s->launches++;
+    FLUID_CUDA(cudaEventRecord(s->ev_out_ready, s->stream));
+    FLUID_CUDA(cudaStreamWaitEvent(s->d2h_stream, s->ev_out_ready, 0));
+    if (cap) FLUID_CUDA(cudaMemcpyAsync(dst, s->aos_out, (size_t)cap * sizeof(FluidParticle), cudaMemcpyDeviceToHost, s->d2h_stream));
+    FLUID_CUDA(cudaMemcpyAsync(info, info_dev, 8, cudaMemcpyDeviceToHost, s->d2h_stream));
+    FLUID_CUDA(cudaEventRecord(s->ev_d2h_done, s->d2h_stream));
+    s->out_used = true;
+    FLUID_CUDA(cudaGetLastError());
+    return FLUID_OK;
+}
+int fluid_multi_sync_transfers(FluidMulti* h) {
+    MULTI_OR_FAIL(h);
+    for (Band* b : m->bands) {
+        int rc = fluid_sim_sync_transfers(reinterpret_cast<FluidSim*>(b->sim));
+        if (rc != FLUID_OK) return rc;
+    }
+    return multi_check_errors(m);
 }
 
 // row bounds with (nearly) equal particle counts per band, from the particles' positions (host arithmetic): for scenes

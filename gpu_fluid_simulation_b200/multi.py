@@ -140,6 +140,18 @@ class MultiFluidSimulation:
                                                        C.byref(n), C.byref(goff)))
         return out[: n.value], goff.value
 
+    def upload_band_async(self, particles):
+        """pinned AoS source; collective; complete after sync_transfers()."""
+        n = int(particles.shape[0])
+        _lib.check(self._lib.fluid_multi_upload_band_async(self._h, _lib.ptr(particles) if n else None, n))
+
+    def download_band_async(self, out, info):
+        """out: pinned AoS array (its length = the copy's capacity); info: pinned uint32[2] <- (size, global offset)."""
+        _lib.check(self._lib.fluid_multi_download_band_async(self._h, _lib.ptr(out), int(out.shape[0]), _lib.ptr(info)))
+
+    def sync_transfers(self):
+        _lib.check(self._lib.fluid_multi_sync_transfers(self._h))
+
     def _rank_of_local(self, local_band):
         return local_band if self.local_bands == self.world else getattr(self, "rank", 0)
 

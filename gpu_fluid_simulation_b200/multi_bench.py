@@ -185,33 +185,46 @@ def run_multi_bench(args, rank, world, local_rank, workloads, algo_bytes, peak, 
     # ---- end to end: every rank uploads its band from pinned host memory, ticks, downloads it --------------------
     e2e = None
     if not args.no_e2e:
-        k = max(1, args.e2e_steps)
-        cap = int(max(counts) * 1.2) + 65536
-        host = torch.empty((cap, 8), dtype=torch.float32).pin_memory()
-        view = host.numpy().view(_lib.PARTICLE_DTYPE).reshape(-1)
-        h2d = d2h = 0
-        got, _ = m.download_band(out=view)
-        n_now = got.shape[0]
+        k = max(2, args.e2e_steps)
+        got, _ = m.download_band()
+        n0 = int(got.shape[0])
+        cap = n0 + 4 * per_row + 4096          # a tick changes a band's size by the few particles that cross its two borders
+        host_in = torch.empty((max(n0, 1), 8), dtype=torch.float32).pin_memory()
+        view_in = host_in.numpy().view(_lib.PARTICLE_DTYPE).reshape(-1)
+        view_in[:n0] = got
+        outs = [torch.empty((cap, 8), dtype=torch.float32).pin_memory() for _ in range(2)]
+        views = [o.numpy().view(_lib.PARTICLE_DTYPE).reshape(-1) for o in outs]
+        infos = [torch.zeros(2, dtype=torch.int32).pin_memory() for _ in range(2)]
+        del got
+        # per step, through the library's pipelined band transfers: upload this rank's band (pinned AoS), tick (with its
+        # exchange), download the band (pinned AoS); the upload of step k+1 runs under the download of step k
+        m.upload_band_async(view_in[:n0]); m.tick(ts); m.download_band_async(views[0], infos[0].numpy().view(np.uint32)); m.sync_transfers()
         dist.barrier()
         t0 = time.perf_counter()
-        for _ in range(k):
-            m.upload_band(view[:n_now])
-            h2d += n_now * 32
+        for j in range(k):
+            m.upload_band_async(view_in[:n0])
             m.tick(ts)
-            got, _ = m.download_band(out=view)  # synchronises
-            n_now = got.shape[0]
-            d2h += n_now * 32
-        m.sync()
+            m.download_band_async(views[j & 1], infos[j & 1].numpy().view(np.uint32))
+        m.sync_transfers()
+        dt_local = time.perf_counter() - t0
         dist.barrier()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dt = torch.tensor([dt_local], dtype=torch.float64, device=f"cuda:{local_rank}")
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        tot = torch.tensor([h2d, d2h], dtype=torch.int64, device=f"cuda:{local_rank}")
+        n_after = int(infos[(k - 1) & 1][0])
+        assert 0 < n_after <= cap, "the download window was too small for the band"
+        # the pipelined download must be what the plain one returns
+        chk, _ = m.download_band()
+        assert chk.shape[0] == n_after and np.array_equal(chk, views[(k - 1) & 1][:n_after]), "pipelined band download differs from the synchronous one"
+        tot = torch.tensor([n0 * 32, cap * 32 + 8, n_after], dtype=torch.int64, device=f"cuda:{local_rank}")
         dist.all_reduce(tot)
-        e2e = {"value": n_total * k / float(dt.item()), "unit": "particle-steps/s", "h2d_bytes_per_step": int(tot[0].item()) // k,
-               "d2h_bytes_per_step": int(tot[1].item()) // k, "steps": k, "ms_per_step": 1e3 * float(dt.item()) / k,
-               "note": "every rank per step: fluid_multi_upload_band (pinned host AoS) + fluid_multi_tick + fluid_multi_download_band "
-                       "(pinned host AoS), all ranks concurrently"}
-        del host, view
+        assert int(tot[2].item()) == n_total, "particles were lost or duplicated in the end-to-end loop"
+        e2e = {"value": n_total * k / float(dt.item()), "unit": "particle-steps/s", "h2d_bytes_per_step": int(tot[0].item()),
+               "d2h_bytes_per_step": int(tot[1].item()), "steps": k, "ms_per_step": 1e3 * float(dt.item()) / k,
+               "rank0_gbs": {"h2d": n0 * 32 * k / dt_local / 1e9, "d2h": cap * 32 * k / dt_local / 1e9},
+               "note": "every rank per step: fluid_multi_upload_band_async (its band, pinned host AoS) + fluid_multi_tick (with the exchange) + "
+                       "fluid_multi_download_band_async (pinned host AoS); one fluid_multi_sync_transfers after the last step; all ranks "
+                       "concurrently, the upload of the next step overlapping the download of the previous one"}
+        del host_in, outs, views, view_in
 
     ms_per_step = ms / args.steps
     ph = dict(phases)

@@ -295,6 +295,14 @@ int fluid_multi_download_particles(FluidMulti* m, FluidParticle* dst);
  * concatenated in rank order. download: the band in key order, its size and its offset in the global key order. */
 int fluid_multi_upload_band(FluidMulti* m, const FluidParticle* band, uint32_t n, const uint32_t* origins);
 int fluid_multi_download_band(FluidMulti* m, int local_band, FluidParticle* dst, uint32_t cap, uint32_t* n_out, uint32_t* global_offset_out);
+/* Pipelined variants for one-rank-per-process handles (as fluid_sim_upload / _download_particles_async: own copy streams and
+ * staging buffers, the upload of the next state overlaps the download of the previous result). Nothing is read back by the
+ * host: the upload's band sizes are all-gathered on the device (origins = rank-order concatenation). download copies the
+ * band's first `cap` particles (key order) and {size, global offset} into info[2]; src, dst and info should be pinned; valid
+ * after fluid_multi_sync_transfers (which also reports latched overflow errors). */
+int fluid_multi_upload_band_async(FluidMulti* m, const FluidParticle* src, uint32_t n);
+int fluid_multi_download_band_async(FluidMulti* m, FluidParticle* dst, uint32_t cap, uint32_t* info);
+int fluid_multi_sync_transfers(FluidMulti* m);
 /* synchronises; counts[r] = particles rank r owns (every rank tracks all of them on the device) */
 int fluid_multi_particle_counts(FluidMulti* m, uint32_t* counts /* world */);
 /* bindings 1 and 2 for the whole domain (start_indices holds GLOBAL sorted indices; one-rank-per-process handles return

@@ -6,7 +6,8 @@
 //! CUDA meaning; the renderer reads particles through `download_particles` (sorted AoS, the same bytes the
 //! reference's vertex/storage buffer holds) or the raw device pointers of `device_view`.
 //!
-//! NOT COMPILED in the build container (no rustc/cargo there); checked only by review against the header.
+//! NOT COMPILED in the build container (no rustc/cargo there); checked by review against the header. The same call
+//! sequence is compiled and run from C (tests/c_abi_host.c, gcc) on the GPU box.
 #![allow(non_camel_case_types)]
 use std::ffi::{c_char, c_int, c_void, CStr};
 
@@ -29,6 +30,11 @@ pub struct TickSettings {
 pub struct FluidObject { pub position: [f32; 2], pub kind: u32, pub pad: u32, pub pad2: [u32; 4] }
 
 #[repr(C)] pub struct FluidSim { _opaque: [u8; 0] }
+#[repr(C)] pub struct FluidMulti { _opaque: [u8; 0] }
+
+/// `FluidMultiOptions` (include/fluid_b200.h); `Default` = equal bands of grid rows, default capacity and windows, transport AUTO
+#[repr(C)] #[derive(Clone, Copy, Default)]
+pub struct FluidMultiOptions { pub row_bounds: [u32; 9], pub capacity: u32, pub window_near: u32, pub window_far: u32, pub transport: i32, pub reserved: [u32; 4] }
 
 extern "C" {
     fn fluid_last_error() -> *const c_char;
@@ -54,6 +60,19 @@ extern "C" {
     fn fluid_sim_download_particles_async(sim: *mut FluidSim, dst: *mut ParticleInstance) -> c_int;
     fn fluid_sim_sync_transfers(sim: *mut FluidSim) -> c_int;
     fn fluid_sim_state_changed(sim: *mut FluidSim) -> c_int;
+    fn fluid_sim_render_frame(sim: *mut FluidSim, inv_proj: *const f32, w: u32, h: u32, rgba8_out: *mut u8, srgb: c_int, wait: c_int) -> c_int;
+    // the multi-GPU step: the same call per frame, every GPU of the box behind it
+    fn fluid_multi_create(settings: *const SimulationSettings, n_ranks: c_int, devices: *const c_int, opt: *const FluidMultiOptions,
+                          out: *mut *mut FluidMulti) -> c_int;
+    fn fluid_multi_destroy(m: *mut FluidMulti);
+    fn fluid_multi_tick(m: *mut FluidMulti, tick: *const TickSettings) -> c_int;
+    fn fluid_multi_sync(m: *mut FluidMulti) -> c_int;
+    fn fluid_multi_tick_count(m: *const FluidMulti) -> u32;
+    fn fluid_multi_upload_particles(m: *mut FluidMulti, all: *const ParticleInstance, n: u32) -> c_int;
+    fn fluid_multi_download_particles(m: *mut FluidMulti, dst: *mut ParticleInstance) -> c_int;
+    fn fluid_multi_download_start_indices(m: *mut FluidMulti, dst: *mut u32) -> c_int;
+    fn fluid_multi_upload_force_field(m: *mut FluidMulti, xy: *const f32) -> c_int;
+    fn fluid_multi_particle_counts(m: *mut FluidMulti, counts: *mut u32) -> c_int;
 }
 
 fn check(rc: c_int) {
@@ -119,6 +138,12 @@ impl FluidSimulation {
         check(unsafe { fluid_sim_render(self.handle, inv_proj.as_ptr(), w, h, std::ptr::null_mut(), img.as_mut_ptr(), std::ptr::null_mut()) });
         img
     }
+    /// the per-frame form: blended image only, optionally sRGB-encoded as the reference's preferred surface format does
+    /// on store (src/renderer.rs:137-140); `wait = false` only enqueues (pinned `img`, complete after `sync`)
+    pub fn render_frame(&mut self, inv_proj: &[f32; 16], w: u32, h: u32, img: &mut [u8], srgb: bool, wait: bool) {
+        assert_eq!(img.len(), (w * h * 4) as usize);
+        check(unsafe { fluid_sim_render_frame(self.handle, inv_proj.as_ptr(), w, h, img.as_mut_ptr(), srgb as c_int, wait as c_int) });
+    }
     /// row f4 — compute.wgsl:300-498 per sorted particle; a diagnostic, not applied (the call at :92 is commented out)
     pub fn surface_tension(&mut self) -> Vec<[f32; 2]> {
         let mut v = vec![[0f32; 2]; self.settings.particle_count as usize];
@@ -147,3 +172,48 @@ impl FluidSimulation {
 }
 
 impl Drop for FluidSimulation { fn drop(&mut self) { unsafe { fluid_sim_destroy(self.handle) } } }
+
+/// `FluidSimulation` over several GPUs of one box: bands of grid rows, one per device, stepped by ONE call per frame like
+/// the reference's `tick` (src/simulation.rs:459, called from src/renderer.rs:415-418). The library enqueues every band's
+/// kernels and the tick's single NCCL exchange itself and reads nothing back; this thread never blocks in `tick`.
+pub struct MultiFluidSimulation { handle: *mut FluidMulti, settings: SimulationSettings, n_ranks: usize, pub tick: u32 }
+unsafe impl Send for MultiFluidSimulation {}
+
+impl MultiFluidSimulation {
+    /// `FluidSimulation::new_multi`: `devices[r]` = CUDA ordinal of rank r (one GPU per rank: NCCL over NVLink)
+    pub fn new_multi(devices: &[i32], settings: SimulationSettings, options: FluidMultiOptions) -> Self {
+        let mut handle = std::ptr::null_mut();
+        check(unsafe { fluid_multi_create(&settings, devices.len() as c_int, devices.as_ptr(), &options, &mut handle) });
+        Self { handle, settings, n_ranks: devices.len(), tick: 0 }
+    }
+    pub fn tick(&mut self, settings: TickSettings) {
+        check(unsafe { fluid_multi_tick(self.handle, &settings) });
+        self.tick = unsafe { fluid_multi_tick_count(self.handle) };
+    }
+    /// `device.poll(Wait)`; panics if a rank latched an overflow (an exchange window or a band's capacity was too small)
+    pub fn sync(&mut self) { check(unsafe { fluid_multi_sync(self.handle) }); }
+    pub fn write_force_field(&mut self, field: &[[f32; 2]]) {
+        assert_eq!(field.len(), (self.settings.texture_size[0] * self.settings.texture_size[1]) as usize);
+        check(unsafe { fluid_multi_upload_force_field(self.handle, field.as_ptr() as *const f32) });
+    }
+    pub fn upload_particles(&mut self, all: &[ParticleInstance]) {
+        check(unsafe { fluid_multi_upload_particles(self.handle, all.as_ptr(), all.len() as u32) });
+    }
+    /// the whole domain in key order: the bytes a single `FluidSimulation` would hold
+    pub fn download_particles(&mut self) -> Vec<ParticleInstance> {
+        let mut v = vec![ParticleInstance::default(); self.settings.particle_count as usize];
+        check(unsafe { fluid_multi_download_particles(self.handle, v.as_mut_ptr()) });
+        v
+    }
+    pub fn download_start_indices(&mut self, cells: usize) -> Vec<u32> {
+        let mut v = vec![0u32; cells];
+        check(unsafe { fluid_multi_download_start_indices(self.handle, v.as_mut_ptr()) });
+        v
+    }
+    pub fn particle_counts(&mut self) -> Vec<u32> {
+        let mut v = vec![0u32; self.n_ranks];
+        check(unsafe { fluid_multi_particle_counts(self.handle, v.as_mut_ptr()) });
+        v
+    }
+}
+impl Drop for MultiFluidSimulation { fn drop(&mut self) { unsafe { fluid_multi_destroy(self.handle) } } }

@@ -184,6 +184,34 @@ def test_many_ticks_without_host_reads(fluid):
         _assert_identical(m.download_particles(), m.download_start_indices(), ref.download_particles(), ref.download_start_indices())
 
 
+def test_pipelined_band_transfers(fluid):
+    """fluid_multi_upload_band_async / _download_band_async on a one-rank handle: same bytes as the synchronous calls and as
+    a plain FluidSim, with nothing read back by the host between upload and download."""
+    import torch
+    from gpu_fluid_simulation_b200 import multi
+    s, ts, p = scenes.uniform_box(200)
+    n = p.shape[0]
+    src = torch.empty((n, 8), dtype=torch.float32).pin_memory()
+    srcv = src.numpy().view(fluid.PARTICLE_DTYPE).reshape(-1)
+    srcv[:] = p
+    dst = torch.empty((n + 64, 8), dtype=torch.float32).pin_memory()
+    dstv = dst.numpy().view(fluid.PARTICLE_DTYPE).reshape(-1)
+    info = torch.zeros(2, dtype=torch.int32).pin_memory()
+    with multi.MultiFluidSimulation.new_rank(0, 1, None, 0, s, capacity=n + 64) as m, fluid.FluidSimulation.new(0, s) as ref:
+        for _ in range(3):  # every round replaces the state, as bench.py's e2e loop does
+            m.upload_band_async(srcv)
+            m.tick_n(ts, 2)
+            m.download_band_async(dstv, info.numpy().view(np.uint32))
+        m.sync_transfers()
+        ref.upload_particles(p)
+        ref.tick_n(ts, 2)
+        want = ref.download_particles()
+        assert int(info[0]) == n and int(info[1]) == 0
+        assert np.array_equal(dstv[:n], want)
+        got, goff = m.download_band()
+        assert goff == 0 and np.array_equal(got, want)
+
+
 def _gpus():
     import torch
     return torch.cuda.device_count()
