@@ -11,7 +11,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import oracle as O  # noqa: E402
 from gpu_fluid_simulation_b200 import SimulationSettings, TickSettings, scenes  # noqa: E402
 
-out = {"nproc": os.cpu_count()}
+out = {"nproc": os.cpu_count(), "affinity": len(os.sched_getaffinity(0))}
+O.lib().oracle_set_num_threads(len(os.sched_getaffinity(0)))
 
 
 def timed_ticks(sim, ts, ticks, **kw):
@@ -37,7 +38,20 @@ sim = O.OracleSim(s, p, sort_mode=O.SORT_COUNTING)
 per = timed_ticks(sim, ts, 5, stop_after=1)
 out["B3_1m_uniform_hash_sort_table"] = {"s_per_step": round(per, 4)}
 
-for size in (1024, 4096):
+# the reference's own shaders (transpiled WGSL, oracle/_ref) with their own dispatch schedule, where the library is there
+from oracle import wgsl_ref as W  # noqa: E402
+if W.available():
+    W.lib().wgslref_set_num_threads(len(os.sched_getaffinity(0)))
+    s, ts = SimulationSettings(), TickSettings()
+    sim = W.WgslRefSim(O, s)
+    per = timed_ticks(sim, ts, 20)
+    out["R1_default_scene_transpiled_wgsl"] = {"s_per_tick": round(per, 5), "particle_steps_per_s": round(s.particle_count / per)}
+    s, ts, p = scenes.dam_break(500, 2000)
+    sim = W.WgslRefSim(O, s, p)
+    per = timed_ticks(sim, ts, 5)
+    out["R2_1m_dam_break_transpiled_wgsl"] = {"s_per_tick": round(per, 4), "particle_steps_per_s": round(s.particle_count / per)}
+
+for size in (1024, 4096, 8192):
     rng = np.random.default_rng(size)
     mask = (rng.random((size, size)) < 0.002).astype(np.uint8) * 255
     if hasattr(O, "jfa_seed_from_mask"):
@@ -50,3 +64,5 @@ for size in (1024, 4096):
         O.generate_smooth_gradient_field(mask)
         out["B5_cpu_field_1024_single_thread"] = {"ms_per_field": round(1e3 * (time.perf_counter() - t0), 1)}
 print(json.dumps(out))
+if os.path.isdir("gpurun_out"):
+    json.dump(out, open("gpurun_out/cpu_baselines.json", "w"), indent=1)
