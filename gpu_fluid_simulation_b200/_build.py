@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "libfluid_b200.so")
 SOURCES = ["fluid_sim.cu", "jfa.cu", "selftest.cu", "render.cu", "dormant.cu"]
-HEADERS = ["multi.inl", "field.inl", "kernels_band.cuh", "common.cuh", "radix_sort.cuh", "kernels_hash.cuh", "kernels_cells.cuh", "kernels_count.cuh", "kernels_sph.cuh", "sim_internal.h",
+HEADERS = ["multi.inl", "field.inl", "kernels_band.cuh", "band_common.cuh", "common.cuh", "radix_sort.cuh", "kernels_hash.cuh", "kernels_cells.cuh", "kernels_count.cuh", "kernels_sph.cuh", "sim_internal.h",
            os.path.join("..", "..", "include", "fluid_b200.h")]
 
 NVCC_FLAGS = [
