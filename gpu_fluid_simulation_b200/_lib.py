@@ -143,6 +143,7 @@ PROTOTYPES = {
     "fluid_multi_balanced_bounds": (_i, [C.POINTER(SimSettings), _P, _u32, _i, _P]),
     "fluid_jfa_run": (_i, [_P, _u32, _u32, _P, _i]),
     "fluid_jfa_pass": (_i, [_P, _u32, _u32, _u32, _P, _i]),
+    "fluid_jfa_run_static": (_i, [_P, _u32, _u32, _P, _i, _P, _i]),
     "fluid_jfa_seed_from_mask": (_i, [_P, _u32, _u32, _P, _i]),
     "fluid_jfa_seed_from_particles": (_i, [_P, _u32, C.POINTER(C.c_float * 2), _u32, _u32, _P, _i]),
     "fluid_jfa_to_force_field": (_i, [_P, _u32, _u32, _P, _i]),

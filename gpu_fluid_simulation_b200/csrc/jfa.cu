@@ -13,6 +13,7 @@
 // fused in ONE kernel that stages a tile plus halo in shared memory and runs those passes there,
 // each pass reading only the previous pass's values (strict ping-pong, as the shader's two bindings).
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -530,5 +531,93 @@ int fluid_sim_jfa_from_particles(FluidSim* h_, uint32_t w, uint32_t h, uint32_t*
 }
 
 }  // extern "C"
+
+// ---- fluid_jfa_run_static: the jump flood for callers that may not allocate ---------------------------------------
+// No counterpart in the reference (see include/fluid_b200.h).
+// The ping-pong images and the boundary staging image of fluid_jfa_run live in ONE file-scope device array instead of
+// three cudaMalloc'ed buffers. Layout (bytes): [0, 4M) packed image a | [4M, 8M) packed image b | [8M, 16M) rg32uint
+// staging image, M = FLUID_JFA_STATIC_MAX_PIXELS. Every GPU that loads the library holds the array until exit.
+// In HOST code `g_jfa_static` is only a handle: its device address comes from cudaGetSymbolAddress, once per device,
+// with that device current (jfa_static_base); kernels are given that address, never the symbol.
+namespace fluid {
+
+constexpr size_t JFA_STATIC_BYTES = (size_t)FLUID_JFA_STATIC_MAX_PIXELS * 16;
+static __device__ __align__(256) unsigned char g_jfa_static[JFA_STATIC_BYTES];
+
+constexpr int JFA_STATIC_MAX_DEVICES = 64;
+static std::mutex g_jfa_static_mutex;
+static unsigned char* g_jfa_static_base[JFA_STATIC_MAX_DEVICES] = {};
+
+// device address of g_jfa_static on `device` (which must be the current device)
+static int jfa_static_base(int device, unsigned char** out) {
+    if (device < 0 || device >= JFA_STATIC_MAX_DEVICES) { set_error("fluid_jfa_run_static: device ordinal out of range"); return FLUID_ERR_NO_DEVICE; }
+    std::lock_guard<std::mutex> lock(g_jfa_static_mutex);
+    if (!g_jfa_static_base[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_jfa_static);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            set_error(std::string("fluid_jfa_run_static: cudaGetSymbolAddress(g_jfa_static) failed: ") + cudaGetErrorString(e));
+            return FLUID_ERR_CUDA;
+        }
+        g_jfa_static_base[device] = static_cast<unsigned char*>(p);
+    }
+    *out = g_jfa_static_base[device];
+    return FLUID_OK;
+}
+
+// can a kernel running on the current device dereference p? (device / managed memory, or mapped pinned host memory;
+// *dev receives the address to hand to the kernel)
+static bool jfa_device_reachable(const void* p, const void** dev) {
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) { *dev = p; return true; }
+    if (a.type == cudaMemoryTypeHost && a.devicePointer) { *dev = a.devicePointer; return true; }
+    return false;
+}
+
+}  // namespace fluid
+
+extern "C" int fluid_jfa_run_static(const uint32_t* seeds_in, uint32_t w, uint32_t h, uint32_t* seeds_out, int device_ordinal,
+                                    void* stream, int wait) {
+    if (!seeds_in || !seeds_out) { set_error("fluid_jfa_run_static: null argument"); return FLUID_ERR_INVALID_ARGUMENT; }
+    int rc = check_image(w, h); if (rc) return rc;
+    const size_t npx = (size_t)w * h;
+    if (npx > (size_t)FLUID_JFA_STATIC_MAX_PIXELS) {
+        set_error("fluid_jfa_run_static: image of " + std::to_string(w) + " x " + std::to_string(h) + " = " + std::to_string(npx) +
+                  " pixels exceeds FLUID_JFA_STATIC_MAX_PIXELS = " + std::to_string(FLUID_JFA_STATIC_MAX_PIXELS) +
+                  " (the static scratch is fixed at build time; use fluid_jfa_run for larger images)");
+        return FLUID_ERR_UNSUPPORTED;
+    }
+    rc = select_device(device_ordinal); if (rc) return rc;
+    unsigned char* base = nullptr;
+    rc = jfa_static_base(device_ordinal, &base); if (rc) return rc;
+    uint32_t* a = reinterpret_cast<uint32_t*>(base);
+    uint32_t* b = reinterpret_cast<uint32_t*>(base + (size_t)FLUID_JFA_STATIC_MAX_PIXELS * 4);
+    uint2* io = reinterpret_cast<uint2*>(base + (size_t)FLUID_JFA_STATIC_MAX_PIXELS * 8);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned blocks = (unsigned)((npx + 255) / 256);
+
+    // inputs / outputs the kernels can reach are used where they lie; plain host memory goes through the staging image
+    const void* in_dev = nullptr;
+    const void* out_dev = nullptr;
+    const bool in_direct = jfa_device_reachable(seeds_in, &in_dev);
+    const bool out_direct = jfa_device_reachable(seeds_out, &out_dev);
+    if (!in_direct) {
+        FLUID_CUDA(cudaMemcpyAsync(io, seeds_in, npx * 8, cudaMemcpyHostToDevice, st));
+        in_dev = io;
+    }
+    // Nothing in the scratch has to start at zero: a[0, npx) is written whole by the pack kernel, every pass writes every
+    // pixel of its destination before the next pass reads it, and the staging image is written whole before it is read.
+    // The canonical-image fast path of fluid_jfa_run needs a flag read back by the host between two launches; this entry
+    // point never waits on the device before its last launch, so it always runs the general kernels (same results).
+    k_pack_rg32<<<blocks, 256, 0, st>>>(static_cast<const uint2*>(in_dev), a, npx, w, nullptr);
+    uint32_t* res = jfa_run_device(a, b, w, h, st, nullptr, false, false);
+    k_unpack_rg32<<<blocks, 256, 0, st>>>(res, out_direct ? static_cast<uint2*>(const_cast<void*>(out_dev)) : io, npx);
+    FLUID_CUDA(cudaGetLastError());
+    if (!out_direct) FLUID_CUDA(cudaMemcpyAsync(seeds_out, io, npx * 8, cudaMemcpyDeviceToHost, st));
+    if (wait || !out_direct || !in_direct) FLUID_CUDA(cudaStreamSynchronize(st));
+    return FLUID_OK;
+}
 
 #include "field.inl"

@@ -339,6 +339,24 @@ int fluid_jfa_seed_from_particles(const FluidParticle* particles, uint32_t n, co
 /* field = -(pixel - seed) as float pairs (sign / zero rule of src/main.rs:493-511). */
 int fluid_jfa_to_force_field(const uint32_t* seeds, uint32_t w, uint32_t h, float* field_xy, int device_ordinal);
 
+/* fluid_jfa_run for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
+ * Same result as fluid_jfa_run, but the two ping-pong images and the staging image live in one file-scope
+ * `static __device__` array of FLUID_JFA_STATIC_MAX_PIXELS * 16 bytes (16 MiB) that every GPU which loads the library
+ * holds until exit; the call makes no cudaMalloc / cudaFree / stream or event creation. Images with
+ * w * h > FLUID_JFA_STATIC_MAX_PIXELS are rejected with FLUID_ERR_UNSUPPORTED (use fluid_jfa_run).
+ *   seeds_in / seeds_out  rg32uint images; device, managed or mapped pinned memory is used where it lies, plain host
+ *                         memory is staged through the static array (the call then returns after the copy back);
+ *   stream                cudaStream_t the work is enqueued on (NULL = the default stream);
+ *   wait                  nonzero: cudaStreamSynchronize(stream) before returning; zero with device pointers: the call
+ *                         only enqueues (nothing is read back by the host in between, so it can be captured).
+ * All calls on one GPU SHARE the array: two calls whose kernels overlap on the device (different streams without an
+ * ordering between them, or several threads) race and produce garbage; serialise them. The array keeps the previous
+ * call's contents; nothing in it needs to start at zero (every byte read by a call was written by that call). */
+#define FLUID_JFA_STATIC_MAX_PIXELS (1u << 20)
+int fluid_jfa_run_static(const uint32_t* seeds_in, uint32_t w, uint32_t h, uint32_t* seeds_out, int device_ordinal,
+                         void* stream /* cudaStream_t */, int wait);
+
 /* Device-resident pipeline: particles of `sim` -> seeds -> JFA -> field, written into
  * caller-provided host buffers if non-null; when into_sim != 0 and (w,h) equals the
  * sim's texture size the field is also installed as the sim's force field.
