@@ -429,7 +429,7 @@ def main():
     # ---- the metric's other sizes (BASELINE.json: "at 1M & 64M particles"), a second or two each --------------------
     if not args.no_also and args.workload == "64m-u":
         also = {}
-        for name, wl, warm, steps in (("1m-u", "1m-u", 20, 400), ("1m-d", "1m-d", 20, 200), ("1m-d after 300 ticks", "1m-d", 320, 200),
+        for name, wl, warm, steps in (("1m-u", "1m-u", 20, 400), ("1m-d", "1m-d", 20, 200), ("1m-d after 300 ticks", "1m-d", 300, 100), ("1m-d after 400 ticks", "1m-d", 400, 100),
                                       ("default (100k, the reference's scene)", "default", 20, 400)):
             s2, ts2, p2 = make_scene(wl)
             with fluid.FluidSimulation.new(local_rank, s2) as sim2:

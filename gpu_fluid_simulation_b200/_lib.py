@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libfluid_b200.so")
+LIB_PATH = os.environ.get("FLUID_B200_LIB") or os.path.join(HERE, "libfluid_b200.so")  # (the override is for A/B runs of experimental builds)
 
 # numpy twins of the C structs (reference layouts: src/simulation.rs:53-135)
 PARTICLE_DTYPE = np.dtype([

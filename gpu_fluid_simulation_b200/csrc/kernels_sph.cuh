@@ -140,6 +140,20 @@ k_tile_plans(const DevParams p, const uint32_t* __restrict__ keys, const uint32_
     if (tile < ntiles) make_tile_plan(p, keys, lb, tile, plans);
 }
 
+// Which tile does CTA b of a neighbour pass compute? With gravity along y the fluid piles up in the first or the last grid
+// rows, i.e. at one END of the row-major key order, and a crowded tile costs up to 40x an ordinary one (candidates per
+// particle = the population of 3x3 cells): in index order the heaviest CTAs would start last and the pass would end on a
+// few SMs (1M dam break after 320 ticks: a schedule model gives 1.6x the balanced makespan, a run with the order reversed
+// confirmed it). So on grids of few waves the CTAs take tiles alternately from both ends towards the middle: whichever end
+// is crowded starts at once, each front still walks neighbouring tiles (L2 reuse of the rows between them). On large grids
+// (hundreds of waves) the tail does not matter and the single front keeps the most reuse: the host leaves the order alone
+// there (BOTH_ENDS is a template parameter of the two kernels, chosen by Sim::tiles_both_ends(): the index-order kernels are compiled as before). A list of heavy tiles built by the plan makers and taken first by the CTAs (two tiles
+// per CTA) was built and measured: the second pass per CTA cost 9 % on the uniform box and won less than this on the dam
+// break; dropped.
+__device__ __forceinline__ uint32_t tile_from_both_ends(uint32_t b, uint32_t first, uint32_t count) {
+    return first + ((b & 1u) ? count - 1u - (b >> 1) : (b >> 1));
+}
+
 // thread 0 of a CTA: read the tile's plan, publish the staging bases, issue the copies.
 // arrays[k] / smem[k] / elem_bytes[k]: the SoA streams to stage (1 for density, 3 for force).
 template <int NARR>
@@ -327,7 +341,7 @@ __device__ __forceinline__ float density_walk_staged(const DevParams& p, uint32_
 // candidates, or a tile that was not staged): the force pass scans as before; bit 30: the tile-plan row group.
 constexpr uint32_t NB_FALLBACK = 0x80000000u, NB_GROUP = 0x40000000u, NB_INDEX = 0x3fffffffu;
 
-template <bool BAND>
+template <bool BAND, bool BOTH_ENDS>
 __global__ void __launch_bounds__(SPH_THREADS)
 k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* __restrict__ keys,
           const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk, float* __restrict__ rho,
@@ -344,15 +358,23 @@ k_density(const DevParams p, const float2* __restrict__ pred_s, const uint32_t* 
     // (BAND is a template parameter so that the single-GPU kernel is compiled exactly as it was without band support)
     const uint32_t r_begin = BAND ? __ldg(band_range) : p.own_begin;
     const uint32_t r_end = BAND ? __ldg(band_range + 1) : p.own_begin + p.n;
-    const uint32_t i0 = (BAND ? 0u : p.own_begin) + blockIdx.x * SPH_THREADS;
-    if (BAND && (i0 + SPH_THREADS <= r_begin || i0 >= r_end)) return;  // (whole CTA)
+    uint32_t tile = blockIdx.x;
+    if (BOTH_ENDS) {
+        // band: the tiles that hold [r_begin, r_end) (tiles count from sorted index 0), the CTAs beyond them have nothing to do
+        const uint32_t t_first = BAND ? r_begin / SPH_THREADS : 0u;
+        const uint32_t t_count = BAND ? (r_end > r_begin ? (r_end + SPH_THREADS - 1u) / SPH_THREADS - t_first : 0u) : gridDim.x;
+        if (BAND && blockIdx.x >= t_count) return;  // (whole CTA)
+        tile = tile_from_both_ends(blockIdx.x, t_first, t_count);
+    }
+    const uint32_t i0 = (BAND ? 0u : p.own_begin) + tile * SPH_THREADS;
+    if (BAND && !BOTH_ENDS && (i0 + SPH_THREADS <= r_begin || i0 >= r_end)) return;  // (whole CTA)
     if (threadIdx.x == 0) {
         mbar_init(&s_bar, 1);
         mbar_fence_init();
         const void* const arrays[1] = {pred_s};
         void* const smem[1] = {s_pred};
         const uint32_t eb[1] = {8u};
-        stage_from_plan<1>(plans + blockIdx.x, arrays, smem, eb, &s_bar, &s_plan);
+        stage_from_plan<1>(plans + tile, arrays, smem, eb, &s_bar, &s_plan);
     }
     const uint32_t i = i0 + threadIdx.x;
     const bool valid = BAND ? (i >= r_begin && i < r_end) : (i < r_end);
@@ -906,7 +928,7 @@ __device__ __forceinline__ void force_walk_masked(const DevParams& p, uint32_t s
     }
 }
 
-template <bool DEBUG, bool EXACT, bool BAND>
+template <bool DEBUG, bool EXACT, bool BAND, bool BOTH_ENDS>
 __global__ void __launch_bounds__(SPH_THREADS, FLUID_FORCE_MIN_CTAS)
 k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const float2* __restrict__ pred_s,
                   const float2* __restrict__ vel_s, const float* __restrict__ rho, const uint32_t* __restrict__ keys,
@@ -932,15 +954,22 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     // (BAND is a template parameter so that the single-GPU kernel is compiled exactly as it was without band support)
     const uint32_t r_begin = BAND ? __ldg(band_range) : p.own_begin;
     const uint32_t r_end = BAND ? __ldg(band_range + 1) : p.own_begin + p.n;
-    const uint32_t i0 = (BAND ? 0u : p.own_begin) + blockIdx.x * SPH_THREADS;
-    if (BAND && (i0 + SPH_THREADS <= r_begin || i0 >= r_end)) return;  // (whole CTA)
+    uint32_t tile = blockIdx.x;
+    const uint32_t t_first = (BOTH_ENDS && BAND) ? r_begin / SPH_THREADS : 0u;
+    const uint32_t t_count = !BOTH_ENDS ? 0u : (BAND ? (r_end > r_begin ? (r_end + SPH_THREADS - 1u) / SPH_THREADS - t_first : 0u) : gridDim.x);
+    if (BOTH_ENDS) {
+        if (BAND && blockIdx.x >= t_count) return;  // (whole CTA)
+        tile = tile_from_both_ends(blockIdx.x, t_first, t_count);
+    }
+    const uint32_t i0 = (BAND ? 0u : p.own_begin) + tile * SPH_THREADS;
+    if (BAND && !BOTH_ENDS && (i0 + SPH_THREADS <= r_begin || i0 >= r_end)) return;  // (whole CTA)
     if (threadIdx.x == 0) {
         mbar_init(&s_bar, 1);
         mbar_fence_init();
         const void* const arrays[3] = {pred_s, vel_s, rho};
         void* const smem[3] = {s_pred, s_vel, s_rho};
         const uint32_t eb[3] = {8u, 8u, 4u};
-        stage_from_plan<3>(plans + blockIdx.x, arrays, smem, eb, &s_bar, &s_plan);
+        stage_from_plan<3>(plans + tile, arrays, smem, eb, &s_bar, &s_plan);
     }
     const uint32_t i = i0 + threadIdx.x;
     const bool valid = BAND ? (i >= r_begin && i < r_end) : (i < r_end);
@@ -958,9 +987,8 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
     }
     const uint32_t ft = __ldg(frame_time);
     const bool tame = wild_stamp != nullptr && __ldg(wild_stamp) != ft;  // common.cuh tame_component
-    const uint32_t out_i = i - r_begin;                          // index in the (ghost-free) state arrays
     const uint32_t goff = p.global_offset + (global_offset_dev ? __ldg(global_offset_dev) : 0u);
-    uint32_t rand_seed = (out_i + goff) * 12u + ft * 69u;  // compute.wgsl:161 (global sorted index)
+    uint32_t rand_seed = (i - r_begin + goff) * 12u + ft * 69u;  // compute.wgsl:161 (global sorted index; i - r_begin = index in the ghost-free state arrays)
     const float pressure = fmul(p.pressure_constant, fsub(dens, p.rest_density));
     ForceAcc acc = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     __syncthreads();
@@ -989,6 +1017,15 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
         }
     }
     float nx = 0.0f, ny = 0.0f, vx = 0.0f, vy = 0.0f;
+    // BOTH_ENDS: the particle's index is derived again from the block index — held across the walk it would cost a register
+    // of the 64 the kernel is capped at (index order needs none: blockIdx.x is free to re-read; the opaque copy keeps the
+    // compiler from merging this with the computation at the top)
+    uint32_t out_i = i - r_begin;
+    if (BOTH_ENDS) {
+        uint32_t b_again = blockIdx.x;
+        asm volatile("" : "+r"(b_again));
+        out_i = (BAND ? 0u : p.own_begin) + tile_from_both_ends(b_again, t_first, t_count) * SPH_THREADS + threadIdx.x - r_begin;
+    }
     if (valid) {
         // compute.wgsl:90-96
         const float fvx = fmul(acc.vx, p.visc_coef), fvy = fmul(acc.vy, p.visc_coef);

@@ -293,7 +293,12 @@ static int band_enqueue_rest(Multi* m, Band* b, const DevParams& p) {
                (const float2*)s->pos_a, (const float2*)s->vel_a, (const uint32_t*)b->origin, b->explicit_origins ? 1 : 0, b->dyn, s->pos_s, s->pred_s,
                s->vel_s, s->start_indices, s->quirk, (const uint32_t*)s->d_frame_time, reinterpret_cast<TilePlan*>(s->tile_plans));
     s->mark("gather+cells");
-    launch_pdl(pdl, k_density<true>, dim3(tiles), dim3(SPH_THREADS), s->stream, p, (const float2*)s->pred_s, (const uint32_t*)s->keys_b, (const uint32_t*)s->lb_view,
+    if (s->tiles_both_ends())
+        launch_pdl(pdl, k_density<true, true>, dim3(tiles), dim3(SPH_THREADS), s->stream, p, (const float2*)s->pred_s, (const uint32_t*)s->keys_b, (const uint32_t*)s->lb_view,
+               (const uint32_t*)s->quirk, s->rho, s->quirk + 2, (const uint32_t*)s->d_frame_time, reinterpret_cast<const TilePlan*>(s->tile_plans),
+               (const uint32_t*)&b->dyn->dens_begin, s->nb_head, s->nb_mask);
+    else
+        launch_pdl(pdl, k_density<true, false>, dim3(tiles), dim3(SPH_THREADS), s->stream, p, (const float2*)s->pred_s, (const uint32_t*)s->keys_b, (const uint32_t*)s->lb_view,
                (const uint32_t*)s->quirk, s->rho, s->quirk + 2, (const uint32_t*)s->d_frame_time, reinterpret_cast<const TilePlan*>(s->tile_plans),
                (const uint32_t*)&b->dyn->dens_begin, s->nb_head, s->nb_mask);
     s->launches += 6;

@@ -54,6 +54,8 @@ struct Sim {
     float spec_delta = 0.0f;
     bool speculate = true;      // FLUID_NO_SPECULATION=1: off
     bool pdl = true;                             // programmatic dependent launch on the tick's kernels (FLUID_NO_PDL=1: off)
+    int tile_order = -1;                         // neighbour passes: -1 by size, 0 index order, 1 from both ends (FLUID_TILE_ORDER=0|1)
+    bool tiles_both_ends() const;                // which instantiation of the two neighbour kernels the tick launches
     uint32_t *cell_tile_sum = nullptr, *cell_tile_max = nullptr;
     float* cell_tile_sq = nullptr;
     uint32_t cell_tiles = 0;

@@ -112,6 +112,23 @@ def test_all_particles_in_one_cell_and_exact_duplicates(fluid, oracle):
     assert stats["floats_bit_exact"], stats
 
 
+@pytest.mark.parametrize("n,extent,sort_mode", [(6000, (0.9, 0.5), 0), (6000, (0.9, 0.5), 1), (40000, (0.5, 0.15), 0)])
+def test_neighbourhoods_larger_than_the_staging_buffer(fluid, oracle, n, extent, sort_mode):
+    """the late dam break in small: cells of hundreds of particles, so the three row spans of a 256-particle tile exceed the
+    staging buffer (kernels_sph.cuh SPH_CAP) and the tile walks global memory — with the accepted-candidate list while
+    every span is shorter than 2^14, with the plain walk beyond (the 40000-particle case: ~13000 per cell). The
+    reference walks any population (compute.wgsl:173-232). Includes exactly coincident particles (RNG directions)."""
+    s = SimulationSettings(particle_count=n, size=(4.0, 4.0), texture_size=(8, 8))
+    rng = np.random.default_rng(n)
+    p = np.zeros(n, dtype=oracle.PARTICLE_DTYPE)
+    p["position"] = np.float32(0.31) + rng.random((n, 2)) * np.array(extent)  # straddles cell boundaries (h = 0.2)
+    p["position"][200:215] = p["position"][3]
+    p["velocity"] = rng.normal(size=(n, 2)) * 0.5
+    p["predicted_position"] = p["position"]
+    stats = _check(fluid, oracle, s, TickSettings(), p, n_ticks=2, tick_count=7, gpu_sort_mode=sort_mode)
+    assert stats["floats_bit_exact"], stats
+
+
 @pytest.mark.parametrize("wild", ["tiny_velocity", "tiny_offset", "huge_mass", "huge_stiffness", "none"])
 def test_range_tested_path_for_wild_inputs(fluid, oracle, wild):
     """the force pass skips most per-pair range tests of its shared-reciprocal divisions when the tick's inputs are
