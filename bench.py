@@ -401,6 +401,30 @@ def main():
                        "one fluid_sim_sync_transfers after the last step; the upload of the next input overlaps the download of the previous result",
                "serial": {"value": n * ks / dt_serial, "ms_per_step": 1e3 * dt_serial / ks, "steps": ks,
                           "note": "upload_particles + tick + download_particles, each call complete before the next"}}
+        # what the copies alone cost on this box: the same bytes, same pinned buffers, no tick, no transposition — one
+        # direction at a time and both at once (the pipelined loop above cannot be faster than the last figure)
+        dev_in = torch.empty((n, 8), dtype=torch.float32, device=f"cuda:{local_rank}")
+        dev_out = torch.empty((n, 8), dtype=torch.float32, device=f"cuda:{local_rank}")
+        s_up, s_dn = torch.cuda.Stream(device=local_rank), torch.cuda.Stream(device=local_rank)
+
+        def copies(up, down, reps=3):
+            torch.cuda.synchronize(local_rank)
+            t0 = time.perf_counter()
+            for j in range(reps):
+                if up:
+                    with torch.cuda.stream(s_up):
+                        dev_in.copy_(host_in, non_blocking=True)
+                if down:
+                    with torch.cuda.stream(s_dn):
+                        host_outs[j & 1].copy_(dev_out, non_blocking=True)
+            torch.cuda.synchronize(local_rank)
+            return 1e3 * (time.perf_counter() - t0) / reps
+
+        copies(True, True, 1)
+        e2e["copy_floor"] = {"h2d_only_ms": copies(True, False), "d2h_only_ms": copies(False, True), "both_at_once_ms": copies(True, True),
+                             "note": "cudaMemcpyAsync of the step's input and output bytes between the same pinned buffers and device memory, nothing else"}
+        e2e["copy_floor"]["e2e_over_floor"] = e2e["ms_per_step"] / e2e["copy_floor"]["both_at_once_ms"]
+        del dev_in, dev_out
         host_out = None
         del host_in, host_outs, out_views, host_out
         # the reference's own per-frame call pattern, for comparison (extra key, NOT the contract's e2e): the particle
