@@ -2,6 +2,7 @@
 through libfluid_b200's own multi-GPU step (fluid_multi_create_rank / fluid_multi_tick: csrc/multi.inl). torch.distributed
 is only the launcher's plumbing here — it hands rank 0's NCCL id to the other ranks, gathers results for the parity check
 and takes the max over the ranks' timings; no torch call sits inside a tick."""
+import os
 import time
 
 import numpy as np
@@ -224,13 +225,41 @@ def run_multi_bench(args, rank, world, local_rank, workloads, algo_bytes, peak, 
                "note": "every rank per step: fluid_multi_upload_band_async (its band, pinned host AoS) + fluid_multi_tick (with the exchange) + "
                        "fluid_multi_download_band_async (pinned host AoS); one fluid_multi_sync_transfers after the last step; all ranks "
                        "concurrently, the upload of the next step overlapping the download of the previous one"}
-        del host_in, outs, views, view_in
+        # what the copies alone cost when every rank moves its band both ways at once (same pinned buffers, no tick, no
+        # transposition): the floor of the loop above on this box
+        dev_in = torch.empty((max(n0, 1), 8), dtype=torch.float32, device=f"cuda:{local_rank}")
+        dev_out = torch.empty((cap, 8), dtype=torch.float32, device=f"cuda:{local_rank}")
+        s_up, s_dn = torch.cuda.Stream(device=local_rank), torch.cuda.Stream(device=local_rank)
+        floor = {}
+        for name, up, down in (("h2d_only_ms", True, False), ("d2h_only_ms", False, True), ("both_at_once_ms", True, True)):
+            torch.cuda.synchronize(local_rank)
+            dist.barrier()
+            t0 = time.perf_counter()
+            for j in range(3):
+                if up:
+                    with torch.cuda.stream(s_up):
+                        dev_in.copy_(host_in, non_blocking=True)
+                if down:
+                    with torch.cuda.stream(s_dn):
+                        outs[j & 1].copy_(dev_out, non_blocking=True)
+            torch.cuda.synchronize(local_rank)
+            t = torch.tensor([(time.perf_counter() - t0) / 3], dtype=torch.float64, device=f"cuda:{local_rank}")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            floor[name] = 1e3 * float(t.item())
+        floor["note"] = "all ranks at once, max over ranks: cudaMemcpyAsync of each band's bytes between the same pinned buffers and device memory, nothing else"
+        floor["e2e_over_floor"] = e2e["ms_per_step"] / floor["both_at_once_ms"]
+        e2e["copy_floor"] = floor
+        del host_in, outs, views, view_in, dev_in, dev_out
 
     ms_per_step = ms / args.steps
     ph = dict(phases)
     dom_ms = ph.get("force+integrate", 0.0)
     n_rank = int(counts[rank])
-    achieved = algo_bytes["force+integrate"] * n_rank / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    # as on one GPU: in steady state the force pass also runs the next tick's key pass (no separate key kernel runs: its
+    # phase is a few microseconds of header writing), so that pass's 28 B per particle are counted with it
+    spec = os.environ.get("FLUID_NO_SPECULATION", "0") != "1" and args.steps > 1
+    dom_bytes = algo_bytes["force+integrate"] + (algo_bytes["predict+key+hist"] if spec else 0)
+    achieved = dom_bytes * n_rank / (dom_ms * 1e-3) / 1e9 if dom_ms > 0 else 0.0
     line = {"metric": "particle-steps/sec", "value": n_total * args.steps / (ms * 1e-3), "unit": "particle-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -244,7 +273,8 @@ def run_multi_bench(args, rank, world, local_rank, workloads, algo_bytes, peak, 
             "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches.item()),
             "roofline": {"bound": "hbm", "kernel": "k_force_integrate (rank 0)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes_per_particle": algo_bytes["force+integrate"], "kernel_ms": dom_ms,
+                         "algorithmic_bytes_per_particle": dom_bytes, "kernel_ms": dom_ms,
+                         "key_pass": "emitted by the previous tick's force pass (its 28 B/particle are counted with force+integrate)" if spec else "own kernel",
                          "share_of_step": dom_ms / ms_per_step if ms_per_step else None,
                          "phases_ms_rank0": {k_: round(v, 5) for k_, v in phases},
                          "phases_source": "second pass of the same K steps with per-phase events (the timed region runs without them)"},
