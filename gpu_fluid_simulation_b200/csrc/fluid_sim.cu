@@ -147,7 +147,7 @@ void Sim::make_uniform(const FluidTickSettings& t, uint32_t tick_value, FluidSim
 
 // tiles from both ends of the key order while the neighbour passes are a few dozen waves of CTAs (kernels_sph.cuh
 // tile_from_both_ends); measured: 1M dam break -13 % early, -21 % after 320 ticks; no gain on the 64M uniform box
-constexpr uint32_t TILES_BOTH_ENDS_MAX = 65536;  // 16M particles: ~110 waves of 592 resident CTAs
+constexpr uint32_t TILES_BOTH_ENDS_MAX = 16384;  // 4M particles: ~28 waves of 592 resident CTAs (balanced scenes pay ~2 % for the order: 1M-U, 8M-particle bands)
 bool Sim::tiles_both_ends() const { return tile_order >= 0 ? tile_order != 0 : capacity / SPH_THREADS <= TILES_BOTH_ENDS_MAX; }
 DevParams Sim::make_params(const FluidSimUniform& u) const {
     DevParams p;
