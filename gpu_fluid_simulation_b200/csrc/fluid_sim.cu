@@ -2,9 +2,12 @@
 //
 // Host-side mirror of the reference's FluidSimulation (src/simulation.rs): owns the particle store
 // (structure of arrays in HBM), the reference-compatible start_indices table, the force-field texture
-// and one CUDA stream, and enqueues the per-tick kernel sequence
-//   predict+key+histogram -> scan -> onesweep x P -> gather+cell tables -> density -> force+integrate
-// in place of the reference's K1, K2, K3 x S(S+1)/2, K4, K5, K6 dispatches (src/simulation.rs:512-537).
+// and one CUDA stream, and enqueues the per-tick kernel sequence in place of the reference's K1, K2, K3 x S(S+1)/2, K4, K5,
+// K6 dispatches (src/simulation.rs:512-537). Default (counting sort over the cells, kernels_count.cuh), steady state:
+//   cell scan (reduce, downsweep; one launch on small grids) -> slots -> rank+gather+cell tables+tile plans -> density
+//   -> force+integrate (which also emits the NEXT tick's keys and per-cell counts) = six launches (five on small grids);
+// the first tick after an upload or a change of delta starts with predict+key+count. Crowded cells or FLUID_SORT_RADIX:
+//   predict+key+histogram -> scan -> onesweep x P -> gather+cell tables -> tile plans -> density -> force+integrate.
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
