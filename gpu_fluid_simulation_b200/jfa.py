@@ -23,6 +23,19 @@ def jfa_run(seeds: np.ndarray, device: int = 0) -> np.ndarray:
     return out
 
 
+JFA_STATIC_MAX_PIXELS = 1 << 20  # FLUID_JFA_STATIC_MAX_PIXELS (include/fluid_b200.h)
+
+
+def jfa_run_static(seeds: np.ndarray, device: int = 0) -> np.ndarray:
+    """fluid_jfa_run_static: the same result as jfa_run, computed in the library's static device scratch (no device
+    allocation in the call; images of at most JFA_STATIC_MAX_PIXELS pixels; calls on one GPU must not overlap)."""
+    seeds = _img(seeds, np.uint32, 2)
+    h, w, _ = seeds.shape
+    out = np.empty_like(seeds)
+    _lib.check(_lib.load().fluid_jfa_run_static(_lib.ptr(seeds), w, h, _lib.ptr(out), device, None, 1))
+    return out
+
+
 def jfa_pass(seeds: np.ndarray, jump: int, device: int = 0) -> np.ndarray:
     seeds = _img(seeds, np.uint32, 2)
     h, w, _ = seeds.shape
