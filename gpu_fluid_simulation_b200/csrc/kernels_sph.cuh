@@ -40,7 +40,7 @@ namespace fluid {
 #endif
 constexpr int SPH_THREADS = FLUID_SPH_THREADS;  // sorted particles per CTA of the neighbour passes (= tile of the staging plans)
 #ifndef FLUID_SPH_CAP
-#define FLUID_SPH_CAP 1536
+#define FLUID_SPH_CAP 1920  // the most that fits 48 KB of static shared memory in the force pass (20 B per candidate + the 10 KB list); 4 CTAs per SM either way
 #endif
 constexpr int SPH_CAP = FLUID_SPH_CAP;  // staged particles per CTA (3 row spans of ~256+2 cells, rounded)
 

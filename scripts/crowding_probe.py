@@ -15,7 +15,7 @@ from gpu_fluid_simulation_b200 import scenes  # noqa: E402
 
 ap = argparse.ArgumentParser()
 ap.add_argument("--ticks", type=int, nargs="+", default=[20, 320])
-ap.add_argument("--cap", type=int, default=1536)
+ap.add_argument("--cap", type=int, default=1920)
 a = ap.parse_args()
 s, ts, p = scenes.dam_break(500, 2000)
 out = []
