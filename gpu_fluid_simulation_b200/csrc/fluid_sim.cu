@@ -591,18 +591,18 @@ void fluid_sim_destroy(FluidSim* h) {
     Sim* s = reinterpret_cast<Sim*>(h);                                  \
     FLUID_CUDA(cudaSetDevice(s->device));
 
-#define NOT_SLAB(s) if ((s)->band) return invalid("handle is a band of a FluidMulti: drive it through fluid_multi_*")
+#define NOT_BAND(s) if ((s)->band) return invalid("handle is a band of a FluidMulti: drive it through fluid_multi_*")
 
 int fluid_sim_tick(FluidSim* h, const FluidTickSettings* t) {
     SIM_OR_FAIL(h);
-    NOT_SLAB(s);
+    NOT_BAND(s);
     if (!t) return invalid("fluid_sim_tick: null settings");
     return s->enqueue_tick(*t, false);
 }
 int fluid_sim_tick_n(FluidSim* h, const FluidTickSettings* t, uint32_t count) {
     SIM_OR_FAIL(h);
     if (!t) return invalid("fluid_sim_tick_n: null settings");
-    NOT_SLAB(s);
+    NOT_BAND(s);
     for (uint32_t k = 0; k < count; k++) {
         int rc = s->enqueue_tick(*t, false);
         if (rc != FLUID_OK) return rc;
@@ -612,7 +612,7 @@ int fluid_sim_tick_n(FluidSim* h, const FluidTickSettings* t, uint32_t count) {
 int fluid_sim_tick_hash_sort_only(FluidSim* h, const FluidTickSettings* t) {
     SIM_OR_FAIL(h);
     if (!t) return invalid("fluid_sim_tick_hash_sort_only: null settings");
-    NOT_SLAB(s);
+    NOT_BAND(s);
     return s->enqueue_tick(*t, true);
 }
 int fluid_sim_sync(FluidSim* h) {
@@ -684,7 +684,7 @@ static int ensure_pipeline(Sim* s) {
 }
 int fluid_sim_upload_particles_async(FluidSim* h, const FluidParticle* src) {
     SIM_OR_FAIL(h);
-    NOT_SLAB(s);
+    NOT_BAND(s);
     if (!src) return invalid("fluid_sim_upload_particles_async: null source");
     int rc = ensure_pipeline(s);
     if (rc != FLUID_OK) return rc;
@@ -704,7 +704,7 @@ int fluid_sim_upload_particles_async(FluidSim* h, const FluidParticle* src) {
 }
 int fluid_sim_download_particles_async(FluidSim* h, FluidParticle* dst) {
     SIM_OR_FAIL(h);
-    NOT_SLAB(s);
+    NOT_BAND(s);
     if (!dst) return invalid("fluid_sim_download_particles_async: null destination");
     int rc = ensure_pipeline(s);
     if (rc != FLUID_OK) return rc;
@@ -888,7 +888,7 @@ int fluid_sim_last_sort_path(const FluidSim* h) { return h ? reinterpret_cast<co
 
 int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
     SIM_OR_FAIL(h);
-    NOT_SLAB(s);
+    NOT_BAND(s);
     if (capacity <= s->capacity) return FLUID_OK;
     FLUID_CUDA(cudaStreamSynchronize(s->stream));
     if (s->h2d_stream) { FLUID_CUDA(cudaStreamSynchronize(s->h2d_stream)); FLUID_CUDA(cudaStreamSynchronize(s->d2h_stream)); }
@@ -939,7 +939,7 @@ int fluid_sim_reserve(FluidSim* h, uint32_t capacity) {
 }
 int fluid_sim_set_particle_count(FluidSim* h, uint32_t n) {
     SIM_OR_FAIL(h);
-    NOT_SLAB(s);
+    NOT_BAND(s);
     if (n < 2 || n > s->capacity) return invalid("fluid_sim_set_particle_count: need 2 <= n <= capacity");
     s->n = n;
     s->cell_max_known = false;

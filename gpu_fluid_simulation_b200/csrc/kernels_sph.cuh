@@ -934,7 +934,7 @@ k_force_integrate(const DevParams p, const float2* __restrict__ pos_s, const flo
                   const float2* __restrict__ vel_s, const float* __restrict__ rho, const uint32_t* __restrict__ keys,
                   const uint32_t* __restrict__ lb, const uint32_t* __restrict__ quirk,
                   const float2* __restrict__ force_field, const uint32_t* __restrict__ frame_time,
-                  const uint32_t* __restrict__ global_offset_dev /* slab mode with device-resolved metadata, else null */,
+                  const uint32_t* __restrict__ global_offset_dev /* multi-GPU band: the global sorted index of its first owned particle, on the device; else null */,
                   const uint32_t* __restrict__ wild_stamp /* null: always take the per-pair range tests */,
                   const TilePlan* __restrict__ plans,
                   float2* __restrict__ pos_out, float2* __restrict__ vel_out, float2* __restrict__ dbg_accel,
