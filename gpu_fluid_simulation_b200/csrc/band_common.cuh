@@ -16,6 +16,7 @@ constexpr int BAND_KEY_THREADS = 256;
 constexpr uint32_t BAND_ERR_WINDOW = 1u;    // more records for one destination than its window holds (records lost)
 constexpr uint32_t BAND_ERR_CAPACITY = 2u;  // natives + received exceed the rank's capacity (records lost)
 constexpr uint32_t BAND_ERR_COUNT = 4u;     // owned count after the sort differs from the migration matrix's (follows 1 / 2)
+constexpr uint32_t BAND_ERR_PEER = 8u;      // PEER transport: another rank's records for this tick did not appear within the time limit
 
 struct BandRows {
     uint32_t bounds[BAND_MAX_RANKS + 1];  // rank r owns grid rows [bounds[r], bounds[r+1])
@@ -26,6 +27,7 @@ struct BandRows {
 // header of one message (outbox -> inbox), BAND_HDR_WORDS words:
 //   [0] records pushed (may exceed the window: the receiver clamps and latches BAND_ERR_WINDOW)
 //   [1] the sender's latched error bits      [2] the sender's native count
+//   [3] the exchange number this header belongs to, stored LAST (PEER transport: the receiver polls it over NVLink)
 //   [4 + r] natives of the sender whose new owner is rank r (the sender's row of the migration matrix)
 // followed by float4 (pos, vel)[cap] and uint32 origin[cap]
 struct BandBoxes {
@@ -126,7 +128,7 @@ __device__ __forceinline__ void band_push_copies(const BandRows& rows, const Ban
 // the counters for the next tick. A kernel of its own (one CTA, launched before the exchange): letting the last CTA of the
 // key pass do it cost one contended atomic per CTA — 0.4 ms per tick when the key pass is the epilogue of the force
 // pass's 125,000 CTAs (32M particles).
-__global__ void k_band_headers(const BandSpec* __restrict__ spec) {
+__global__ void k_band_headers(const BandSpec* __restrict__ spec, uint32_t stamp) {
     pdl_enter();
     const BandRows rows = spec->rows;
     BandDyn* dyn = spec->dyn;
@@ -143,8 +145,12 @@ __global__ void k_band_headers(const BandSpec* __restrict__ spec) {
     __syncwarp((1u << rows.world) - 1u);
     if (d != me) {
         uint32_t* h = spec->out.box[d];
-        h[0] = cnt; h[1] = err; h[2] = n_nat; h[3] = 0u;
+        h[0] = cnt; h[1] = err; h[2] = n_nat;
         for (int r = 0; r < BAND_MAX_RANKS; r++) h[4 + r] = r < rows.world ? dyn->e_sent[r] : 0u;
+        // the records were stored by an earlier kernel of this stream (complete, hence in L2, which is where a peer's loads
+        // over NVLink are served from); the header words above must be ordered before the stamp for an observer on another GPU
+        __threadfence_system();
+        *reinterpret_cast<volatile uint32_t*>(h + 3) = stamp;
     }
 }
 

@@ -265,4 +265,50 @@ __global__ void k_band_copy_box(const uint4* __restrict__ src, uint4* __restrict
     if (i < (cnt + 3u) / 4u) dst[org16 + i] = src[org16 + i];
 }
 
+// ---- PEER transport: one rank per process, the other ranks' outboxes mapped through CUDA IPC -----------------------
+// The exchange of a tick is a PULL over NVLink: the receiver waits until the sender's header carries this exchange's number
+// (k_band_headers stores it last), then copies the header and the records that are there — not the whole window, as the
+// fixed-size NCCL messages must. Outboxes are double-buffered by exchange parity, so a sender never waits for a receiver:
+// the buffer it fills for exchange x + 1 was last read in exchange x - 1, which every peer finished before it stored
+// the header of exchange x that this rank has already waited for.
+struct PeerBoxes { const uint32_t* box[BAND_MAX_RANKS]; };  // rank s's outbox for this rank (this exchange's parity), null for itself
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint64_t global_timer_ns() {
+    uint64_t t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// one thread per source rank polls that rank's header; a rank that does not show up within the limit latches BAND_ERR_PEER
+// (the pull then copies whatever count the stale header holds, clamped to the window: memory-safe, and the error is reported)
+__global__ void k_band_wait_peers(const PeerBoxes src, int world, int me, uint32_t stamp, BandDyn* __restrict__ dyn, uint64_t limit_ns) {
+    const int s = threadIdx.x;
+    if (s >= world || s == me) return;
+    const uint32_t* flag = src.box[s] + 3;
+    const uint64_t t0 = global_timer_ns();
+    while (ld_acquire_sys(flag) != stamp) {
+        if (global_timer_ns() - t0 > limit_ns) { atomicOr(&dyn->error, BAND_ERR_PEER); break; }
+        __nanosleep(200);
+    }
+}
+// grid (chunks, world): header, posvel[count], origin[count] of every source into this rank's inboxes
+__global__ void k_band_pull(const PeerBoxes src, const BandBoxes in, int me) {
+    const int s = blockIdx.y;
+    if (s == me) return;
+    const uint4* from = reinterpret_cast<const uint4*>(src.box[s]);
+    uint4* to = reinterpret_cast<uint4*>(in.box[s]);
+    const uint32_t cap = in.cap[s];
+    const uint32_t cnt = min(__ldcv(src.box[s]), cap);
+    const uint32_t hdr16 = BAND_HDR_WORDS / 4;
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < hdr16) to[i] = __ldcv(from + i);
+    if (i < cnt) to[hdr16 + i] = __ldcv(from + hdr16 + i);
+    const uint32_t org16 = hdr16 + cap;
+    if (i < (cnt + 3u) / 4u) to[org16 + i] = __ldcv(from + org16 + i);
+}
+
 }  // namespace fluid

@@ -81,6 +81,10 @@ struct Band {
     BandDyn* dyn = nullptr;
     uint8_t* box_mem = nullptr;
     BandBoxes out{}, in{};
+    BandBoxes out_alt{};               // PEER transport: the outboxes of odd exchanges (double buffering); else = out
+    BandSpec* spec_dev_alt = nullptr;  // ... and the device-resident spec that points at them (else = spec_dev)
+    void* peer_base[BAND_MAX_RANKS] = {};  // PEER: the other ranks' box memory, opened through CUDA IPC
+    PeerBoxes peer_out[2] = {};            // PEER: rank s's outbox for this rank, by exchange parity
     uint32_t recv_slots = 0;
     bool explicit_origins = false;  // the next tick is the first after an upload: natives carry explicit origins
     cudaEvent_t ev_key = nullptr, ev_copied = nullptr;
@@ -105,6 +109,7 @@ struct Multi {
     uint32_t tick = 0;
     bool copies_pending = false;  // LOCAL transport: the previous tick's pull kernels have been enqueued
     uint32_t n_total = 0;
+    uint32_t xseq = 0;  // exchanges so far (= ticks enqueued on this handle); never rewound, the same on every rank
 };
 
 int sim_create_internal(const FluidSimSettings* s, int device_ordinal, uint32_t capacity, bool lattice, Sim** out);
@@ -119,6 +124,8 @@ static void band_free(Band* b) {
         if (b->dyn) cudaFree(b->dyn);
         if (b->box_mem) cudaFree(b->box_mem);
         if (b->scratch_word) cudaFree(b->scratch_word);
+        for (int r = 0; r < BAND_MAX_RANKS; r++) if (b->peer_base[r]) cudaIpcCloseMemHandle(b->peer_base[r]);
+        if (b->spec_dev_alt && b->spec_dev_alt != b->spec_dev) cudaFree(b->spec_dev_alt);
         if (b->spec_dev) cudaFree(b->spec_dev);
         if (b->ev_key) cudaEventDestroy(b->ev_key);
         if (b->ev_copied) cudaEventDestroy(b->ev_copied);
@@ -128,6 +135,23 @@ static void band_free(Band* b) {
 }
 
 static uint32_t round_up4(uint32_t v) { return (v + 3u) & ~3u; }
+
+// Exchange windows of a rank: per other rank r, in rank order, [outbox | inbox | second outbox] of the same size. The layout is a
+// function of (world, rank, window sizes) only, so that a rank can address another rank's boxes inside its IPC-mapped block.
+static uint32_t band_window_cap(const Multi* m, int rank, int r) {
+    return round_up4((r == rank - 1 || r == rank + 1) ? m->window_near : m->window_far);
+}
+static size_t band_box_slot_bytes(const Multi* m, int rank, int r) { return (band_box_bytes(band_window_cap(m, rank, r)) + 255) & ~(size_t)255; }
+static size_t band_box_offset(const Multi* m, int rank, int r, int which /* 0 out, 1 in, 2 second out */) {
+    size_t at = 0;
+    for (int q = 0; q < r; q++) if (q != rank) at += 3 * band_box_slot_bytes(m, rank, q);
+    return at + (size_t)which * band_box_slot_bytes(m, rank, r);
+}
+static size_t band_box_mem_bytes(const Multi* m, int rank) {
+    size_t at = 0;
+    for (int q = 0; q < m->world; q++) if (q != rank) at += 3 * band_box_slot_bytes(m, rank, q);
+    return at;
+}
 
 // the band of `rank`: arrays, cell table rows, windows
 static int band_create(Multi* m, int rank, int device, uint32_t capacity, Band** out) {
@@ -148,7 +172,7 @@ static int band_create(Multi* m, int rank, int device, uint32_t capacity, Band**
     uint32_t recv = 0;
     for (int r = 0; r < m->world; r++) {
         if (r == rank) continue;
-        const uint32_t cap = round_up4((r == rank - 1 || r == rank + 1) ? m->window_near : m->window_far);
+        const uint32_t cap = band_window_cap(m, rank, r);
         b->out.cap[r] = b->in.cap[r] = cap;
         recv += cap;
     }
@@ -167,17 +191,16 @@ static int band_create(Multi* m, int rank, int device, uint32_t capacity, Band**
     FLUID_CUDA(cudaMalloc(&b->dyn, sizeof(BandDyn)));
     FLUID_CUDA(cudaMemsetAsync(b->dyn, 0, sizeof(BandDyn), s->stream));
     FLUID_CUDA(cudaMalloc(&b->scratch_word, 128));  // [0] this band's size, [4..12) the gathered sizes, [12..14) download info
-    size_t bytes = 0;
-    for (int r = 0; r < m->world; r++) if (r != rank) bytes += 2 * ((band_box_bytes(b->out.cap[r]) + 255) & ~(size_t)255);
+    const size_t bytes = band_box_mem_bytes(m, rank);
+    b->out_alt = b->out;  // (caps; the boxes follow)
     if (bytes) {
         FLUID_CUDA(cudaMalloc(&b->box_mem, bytes));
         FLUID_CUDA(cudaMemsetAsync(b->box_mem, 0, bytes, s->stream));
-        uint8_t* at = b->box_mem;
         for (int r = 0; r < m->world; r++) {
             if (r == rank) continue;
-            const size_t sz = (band_box_bytes(b->out.cap[r]) + 255) & ~(size_t)255;
-            b->out.box[r] = reinterpret_cast<uint32_t*>(at); at += sz;
-            b->in.box[r] = reinterpret_cast<uint32_t*>(at); at += sz;
+            b->out.box[r] = reinterpret_cast<uint32_t*>(b->box_mem + band_box_offset(m, rank, r, 0));
+            b->in.box[r] = reinterpret_cast<uint32_t*>(b->box_mem + band_box_offset(m, rank, r, 1));
+            b->out_alt.box[r] = reinterpret_cast<uint32_t*>(b->box_mem + band_box_offset(m, rank, r, 2));
         }
     }
     {
@@ -186,6 +209,9 @@ static int band_create(Multi* m, int rank, int device, uint32_t capacity, Band**
         spec.rows = b->rows; spec.out = b->out; spec.dyn = b->dyn; spec.key_lo = b->key_lo; spec.last_bin = b->last_bin;
         FLUID_CUDA(cudaMalloc(&b->spec_dev, sizeof spec));
         FLUID_CUDA(cudaMemcpyAsync(b->spec_dev, &spec, sizeof spec, cudaMemcpyHostToDevice, s->stream));
+        spec.out = b->out_alt;
+        FLUID_CUDA(cudaMalloc(&b->spec_dev_alt, sizeof spec));
+        FLUID_CUDA(cudaMemcpyAsync(b->spec_dev_alt, &spec, sizeof spec, cudaMemcpyHostToDevice, s->stream));
         FLUID_CUDA(cudaStreamSynchronize(s->stream));
     }
     FLUID_CUDA(cudaEventCreateWithFlags(&b->ev_key, cudaEventDisableTiming));
@@ -236,6 +262,10 @@ static int band_set_counts(Band* b, const uint32_t* n_all) {
 }
 
 // ---- the tick, in two halves around the exchange ---------------------------------------------------------
+// the spec (hence the outboxes) the key pass of exchange `seq` fills: PEER alternates between two sets
+static BandSpec* band_spec_of(const Multi* m, const Band* b, uint32_t seq) {
+    return (m->transport == FLUID_TRANSPORT_PEER && (seq & 1u)) ? b->spec_dev_alt : b->spec_dev;
+}
 static int band_enqueue_key(Multi* m, Band* b, const FluidTickSettings& t, DevParams* p_out) {
     Sim* s = b->sim;
     FLUID_CUDA(cudaSetDevice(s->device));
@@ -257,12 +287,12 @@ static int band_enqueue_key(Multi* m, Band* b, const FluidTickSettings& t, DevPa
         const uint32_t max_blocks = (uint32_t)s->num_sms * 8u;
         if (blocks > max_blocks) blocks = max_blocks;
         if (blocks == 0) blocks = 1;
-        launch_pdl(s->pdl, k_band_key, dim3(blocks), dim3(BAND_KEY_THREADS), s->stream, p, (const BandSpec*)b->spec_dev, (const float2*)s->pos_a,
+        launch_pdl(s->pdl, k_band_key, dim3(blocks), dim3(BAND_KEY_THREADS), s->stream, p, (const BandSpec*)band_spec_of(m, b, m->xseq), (const float2*)s->pos_a,
                    (const float2*)s->vel_a, s->keys_u, s->cell_count, (const uint32_t*)(b->explicit_origins ? b->origin : nullptr));
         s->launches++;
     }
     b->count_dirty = false;
-    launch_pdl(s->pdl, k_band_headers, dim3(1), dim3(32), s->stream, (const BandSpec*)b->spec_dev);
+    launch_pdl(s->pdl, k_band_headers, dim3(1), dim3(32), s->stream, (const BandSpec*)band_spec_of(m, b, m->xseq), m->xseq);
     s->launches++;
     s->mark("predict+key+hist");
     FLUID_CUDA(cudaGetLastError());
@@ -312,7 +342,7 @@ static int band_enqueue_rest(Multi* m, Band* b, const DevParams& p) {
         for (Band* d : m->bands) if (d != b) FLUID_CUDA(cudaStreamWaitEvent(s->stream, d->ev_copied, 0));
     }
     launch_force(s, p, tiles, s->pos_a, s->vel_a, pdl, spec ? s->keys_u : nullptr, spec ? count_next : nullptr, &b->dyn->own_begin, &b->dyn->goff,
-                 spec ? b->spec_dev : nullptr);
+                 spec ? band_spec_of(m, b, m->xseq + 1u) : nullptr);
     if (spec) { b->spec_valid = true; b->count_dirty = true; b->spec_delta = s->last_uniform.delta; }
     s->mark("force+integrate");
     if (s->timing) { s->marks_per_tick = s->n_marks; s->timed_ticks++; }
@@ -321,6 +351,7 @@ static int band_enqueue_rest(Multi* m, Band* b, const DevParams& p) {
     return FLUID_OK;
 }
 
+constexpr uint64_t PEER_WAIT_LIMIT_NS = 30ull * 1000 * 1000 * 1000;  // a rank that is 30 s late is reported as lost
 static int multi_exchange(Multi* m) {
     if (m->world == 1) return FLUID_OK;
     if (m->transport == FLUID_TRANSPORT_LOCAL) {
@@ -341,6 +372,19 @@ static int multi_exchange(Multi* m) {
         FLUID_CUDA(cudaGetLastError());
         return FLUID_OK;
     }
+    if (m->transport == FLUID_TRANSPORT_PEER) {
+        Band* b = m->bands[0];
+        Sim* s = b->sim;
+        const int me = b->rows.rank;
+        uint32_t cap_max = 16;
+        for (int r = 0; r < m->world; r++) if (r != me) cap_max = std::max(cap_max, b->in.cap[r]);
+        const PeerBoxes& src = b->peer_out[m->xseq & 1u];
+        k_band_wait_peers<<<1, 32, 0, s->stream>>>(src, m->world, me, m->xseq, b->dyn, PEER_WAIT_LIMIT_NS);
+        k_band_pull<<<dim3((cap_max + 255) / 256, m->world), 256, 0, s->stream>>>(src, b->in, me);
+        s->launches += 2;
+        FLUID_CUDA(cudaGetLastError());
+        return FLUID_OK;
+    }
     FLUID_NCCL(g_nccl.GroupStart());
     for (Band* b : m->bands) {
         const int me = b->rows.rank;
@@ -357,6 +401,7 @@ static int multi_exchange(Multi* m) {
 
 static int multi_enqueue_tick(Multi* m, const FluidTickSettings& t) {
     m->tick += 1;  // src/simulation.rs:460
+    m->xseq += 1;
     DevParams params[BAND_MAX_RANKS];
     if (m->transport == FLUID_TRANSPORT_LOCAL && m->copies_pending) {
         // a source may overwrite its outboxes once every destination has pulled the previous tick's records
@@ -459,6 +504,53 @@ static int multi_upload_all(Multi* m, const FluidParticle* all, uint32_t n) {
     return FLUID_OK;
 }
 
+// PEER transport set-up (collective over the ranks of fluid_multi_create_rank): export this rank's box memory through CUDA
+// IPC, all-gather the handles over NCCL, open the others', all-gather who succeeded; PEER only if everybody did.
+static int band_open_peers(Multi* m, Band* b) {
+    Sim* s = b->sim;
+    const int me = b->rows.rank, world = m->world;
+    FLUID_CUDA(cudaSetDevice(s->device));
+    FLUID_CUDA(cudaStreamSynchronize(s->stream));  // the boxes are zeroed before anybody can look at them
+    constexpr size_t HB = sizeof(cudaIpcMemHandle_t);
+    static_assert(HB == 64, "cudaIpcMemHandle_t");
+    uint8_t* dev = nullptr;
+    FLUID_CUDA(cudaMalloc(&dev, HB * (BAND_MAX_RANKS + 1) + 64 * (BAND_MAX_RANKS + 1)));
+    uint8_t* dev_ok = dev + HB * (BAND_MAX_RANKS + 1);
+    cudaIpcMemHandle_t mine;
+    memset(&mine, 0, sizeof mine);
+    uint32_t ok = (b->box_mem && cudaIpcGetMemHandle(&mine, b->box_mem) == cudaSuccess) ? 1u : 0u;
+    cudaGetLastError();
+    std::vector<cudaIpcMemHandle_t> all(world);
+    auto cleanup = [&](int code) { cudaFree(dev); return code; };
+    if (cudaMemcpyAsync(dev, &mine, HB, cudaMemcpyHostToDevice, s->stream) != cudaSuccess) return cleanup(FLUID_ERR_CUDA);
+    { ncclResult_t r = g_nccl.AllGather(dev, dev + HB, HB, ncclChar, b->comm, s->stream); if (r != ncclSuccess) return cleanup(nccl_fail(r, "ncclAllGather (IPC handles)")); }
+    if (cudaMemcpyAsync(all.data(), dev + HB, HB * world, cudaMemcpyDeviceToHost, s->stream) != cudaSuccess || cudaStreamSynchronize(s->stream) != cudaSuccess) return cleanup(FLUID_ERR_CUDA);
+    if (ok) {
+        for (int r = 0; r < world && ok; r++) {
+            if (r == me) continue;
+            if (cudaIpcOpenMemHandle(&b->peer_base[r], all[r], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); b->peer_base[r] = nullptr; ok = 0; }
+        }
+    }
+    uint32_t oks[BAND_MAX_RANKS] = {};
+    if (cudaMemcpyAsync(dev_ok, &ok, 4, cudaMemcpyHostToDevice, s->stream) != cudaSuccess) return cleanup(FLUID_ERR_CUDA);
+    { ncclResult_t r = g_nccl.AllGather(dev_ok, dev_ok + 64, 1, ncclUint32, b->comm, s->stream); if (r != ncclSuccess) return cleanup(nccl_fail(r, "ncclAllGather (IPC status)")); }
+    if (cudaMemcpyAsync(oks, dev_ok + 64, 4 * world, cudaMemcpyDeviceToHost, s->stream) != cudaSuccess || cudaStreamSynchronize(s->stream) != cudaSuccess) return cleanup(FLUID_ERR_CUDA);
+    bool everybody = true;
+    for (int r = 0; r < world; r++) everybody = everybody && oks[r] == 1u;
+    if (!everybody) {
+        for (int r = 0; r < world; r++) if (b->peer_base[r]) { cudaIpcCloseMemHandle(b->peer_base[r]); b->peer_base[r] = nullptr; }
+        return cleanup(FLUID_OK);  // stays on NCCL
+    }
+    for (int r = 0; r < world; r++) {
+        if (r == me) continue;
+        const uint8_t* base = static_cast<const uint8_t*>(b->peer_base[r]);
+        b->peer_out[0].box[r] = reinterpret_cast<const uint32_t*>(base + band_box_offset(m, r, me, 0));
+        b->peer_out[1].box[r] = reinterpret_cast<const uint32_t*>(base + band_box_offset(m, r, me, 2));
+    }
+    m->transport = FLUID_TRANSPORT_PEER;
+    return cleanup(FLUID_OK);
+}
+
 static int multi_check_errors(Multi* m) {
     for (Band* b : m->bands) {
         FLUID_CUDA(cudaSetDevice(b->sim->device));
@@ -467,7 +559,8 @@ static int multi_check_errors(Multi* m) {
         if (err) {
             char buf[256];
             snprintf(buf, sizeof buf, "fluid_multi: rank %d latched error bits 0x%x (1: an exchange window overflowed, 2: band capacity exceeded, "
-                     "4: particle count mismatch) - particles were lost; recreate with larger windows / capacity", b->rows.rank, err);
+                     "4: particle count mismatch - particles were lost; recreate with larger windows / capacity; 8: a peer's records did not arrive "
+                     "within 30 s)", b->rows.rank, err);
             set_error(buf);
             return FLUID_ERR_OVERFLOW;
         }
@@ -580,6 +673,9 @@ int fluid_multi_create_rank(const FluidSimSettings* s, int rank, int world, cons
     if (rc != FLUID_OK) return fail(rc);
     m->single_process = false;
     if (m->transport == FLUID_TRANSPORT_LOCAL && world > 1) { set_error("fluid_multi_create_rank: FLUID_TRANSPORT_LOCAL needs all ranks in one process"); return fail(FLUID_ERR_INVALID_ARGUMENT); }
+    const char* no_peer = getenv("FLUID_MULTI_NO_PEER");
+    const bool want_peer = world > 1 && (m->transport == FLUID_TRANSPORT_PEER || (m->transport == FLUID_TRANSPORT_AUTO && !(no_peer && no_peer[0] == '1')));
+    const bool need_peer = m->transport == FLUID_TRANSPORT_PEER;
     m->transport = FLUID_TRANSPORT_NCCL;
     Band* b = nullptr;
     rc = band_create(m, rank, device, default_capacity(m, opt), &b);
@@ -592,6 +688,11 @@ int fluid_multi_create_rank(const FluidSimSettings* s, int rank, int world, cons
         cudaSetDevice(device);
         ncclResult_t r = g_nccl.CommInitRank(&b->comm, world, id, rank);
         if (r != ncclSuccess) return fail(nccl_fail(r, "ncclCommInitRank"));
+        if (want_peer) {
+            rc = band_open_peers(m, b);  // collective: every rank takes the same decision
+            if (rc != FLUID_OK) return fail(rc);
+            if (need_peer && m->transport != FLUID_TRANSPORT_PEER) { set_error("fluid_multi_create_rank: FLUID_TRANSPORT_PEER asked for, but CUDA IPC between the ranks is not available"); return fail(FLUID_ERR_UNSUPPORTED); }
+        }
     }
     // every band starts empty: the caller uploads its band (fluid_multi_upload_band)
     uint32_t zeros[BAND_MAX_RANKS] = {};

@@ -13,7 +13,8 @@ from . import _lib
 from ._lib import PARTICLE_DTYPE
 from .simulation import SimulationSettings, TickSettings
 
-TRANSPORT_AUTO, TRANSPORT_NCCL, TRANSPORT_LOCAL = 0, 1, 2
+TRANSPORT_AUTO, TRANSPORT_NCCL, TRANSPORT_LOCAL, TRANSPORT_PEER = 0, 1, 2, 3
+TRANSPORT_NAMES = {0: "auto", 1: "nccl", 2: "local", 3: "peer (CUDA IPC pull over NVLink)"}
 MATH_EXACT, MATH_FAST = 0, 1
 
 

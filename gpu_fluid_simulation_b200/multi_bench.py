@@ -80,6 +80,7 @@ def parity_vs_single_gpu(dist, rank, world, local_rank, kind, arg, ticks=3, math
     m = new_rank_sim(dist, rank, world, local_rank, s, row_bounds=bounds, **opt)
     try:
         m.set_math_mode(math_mode)
+        transport = multi.TRANSPORT_NAMES.get(m.transport, str(m.transport))
         m.upload_band(band)
         m.tick_n(ts, ticks)
         m.sync()
@@ -110,7 +111,7 @@ def parity_vs_single_gpu(dist, rank, world, local_rank, kind, arg, ticks=3, math
             for f in ("grid", "predicted_position", "density", "velocity", "position"):
                 diffs += int((got_all[f] != want[f]).sum())
             diffs += int((table_all != want_table).sum())
-        res = {"scene": f"{kind}:{arg}", "particles": int(want.shape[0]), "ticks": ticks, "fields_differing": diffs}
+        res = {"scene": f"{kind}:{arg}", "particles": int(want.shape[0]), "ticks": ticks, "fields_differing": diffs, "transport": transport}
     flag = torch.tensor([0 if res is None else res["fields_differing"]], dtype=torch.int64, device=f"cuda:{local_rank}")
     dist.broadcast(flag, 0)
     return res, int(flag.item())
@@ -264,8 +265,9 @@ def run_multi_bench(args, rank, world, local_rank, workloads, algo_bytes, peak, 
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload, "particles": n_total, "math": args.math,
-                       "parallelism": f"{world} bands of grid rows, one rank per GPU; the whole step incl. its one NCCL exchange per tick "
-                                      "(2 ghost rows + migrants per neighbour, fixed windows) runs inside libfluid_b200 (fluid_multi_tick); no host read per tick",
+                       "parallelism": f"{world} bands of grid rows, one rank per GPU; the whole step incl. its one exchange per tick "
+                                      "(2 ghost rows + migrants per neighbour) runs inside libfluid_b200 (fluid_multi_tick); no host read per tick",
+                       "transport": multi.TRANSPORT_NAMES.get(m.transport, str(m.transport)),
                        "row_bounds": bounds, "particles_per_rank_start": None, "particles_per_rank_end": counts,
                        "imbalance_end": round(max(counts) * world / n_total, 4),
                        "l2": "inputs larger than L2 (no flush)" if n_total * 64 / world > 252e6 else "per-rank state fits L2; steps run back to back (no flush)"},

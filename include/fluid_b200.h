@@ -251,9 +251,12 @@ int fluid_sim_set_particle_count(FluidSim* sim, uint32_t n);
  *   fluid_multi_create_rank  one rank per process (torchrun / mpirun style); the ranks share fluid_multi_unique_id's bytes
  * Errors that only the device can see (an exchange window or a band's capacity overflowed) are latched there and reported
  * as FLUID_ERR_OVERFLOW by the next call that synchronises (fluid_multi_sync, downloads). */
-#define FLUID_TRANSPORT_AUTO 0   /* NCCL when every rank has its own GPU, LOCAL when ranks share one */
+#define FLUID_TRANSPORT_AUTO 0   /* one process: NCCL when every rank has its own GPU, LOCAL when ranks share one; one rank per process: PEER if CUDA IPC works between all ranks, else NCCL */
 #define FLUID_TRANSPORT_NCCL 1   /* one ncclGroup of send/recv windows per tick (NCCL over NVLink / NVSwitch) */
 #define FLUID_TRANSPORT_LOCAL 2  /* ranks of ONE process: pull kernels over peer-mapped (or the same GPU's) memory, ordered by events */
+#define FLUID_TRANSPORT_PEER 3   /* one rank per process (fluid_multi_create_rank): the other ranks' outboxes mapped through CUDA IPC; each rank
+                                    pulls the records that are there over NVLink once the sender's header carries the tick's exchange number
+                                    (NCCL is still used to set up and for the size all-gather of an upload) */
 #define FLUID_MULTI_MAX_RANKS 8
 #define FLUID_MULTI_ID_BYTES 128 /* sizeof(ncclUniqueId) */
 typedef struct FluidMultiOptions {

@@ -27,7 +27,7 @@ res, bad = multi_bench.parity_vs_single_gpu(dist, rank, world, local_rank, kind,
                                             **({"window_near": 65536} if a.dam else {}))
 if rank == 0:
     print(json.dumps(res), flush=True)
-    print(f"world {world} fields_differing {res['fields_differing']}", flush=True)
+    print(f"world {world} fields_differing {res['fields_differing']} transport {res['transport']}", flush=True)
 dist.barrier()
 dist.destroy_process_group()
 sys.exit(0 if bad == 0 else 1)

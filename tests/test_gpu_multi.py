@@ -231,14 +231,19 @@ def test_nccl_single_process_two_gpus(fluid):
     _assert_identical(got, table, want, want_table)
 
 
-def test_nccl_one_rank_per_process(fluid):
-    """torchrun, one rank per GPU: scripts/multi_parity.py gathers the bands on rank 0 and compares with one GPU."""
+@pytest.mark.parametrize("transport", ["peer", "nccl"])
+@pytest.mark.parametrize("dam", [False, True])
+def test_one_rank_per_process(fluid, transport, dam):
+    """torchrun, one rank per GPU: scripts/multi_parity.py gathers the bands on rank 0 and compares with one GPU. The
+    exchange is the CUDA-IPC pull over NVLink by default (FLUID_TRANSPORT_PEER) and NCCL send/recv with FLUID_MULTI_NO_PEER=1."""
     n = _gpus()
     if n < 2:
         pytest.skip("needs 2 GPUs")
     world = 2 if n < 4 else 4
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
-           "--master-port", "29631", os.path.join(ROOT, "scripts", "multi_parity.py"), "--n-side", "1024", "--ticks", "4"]
-    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+           "--master-port", "29631", os.path.join(ROOT, "scripts", "multi_parity.py"), "--n-side", "1024", "--ticks", "7"] + (["--dam"] if dam else [])
+    env = dict(os.environ, FLUID_MULTI_NO_PEER="1" if transport == "nccl" else "0")
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert "fields_differing 0" in res.stdout
+    assert f"transport {transport}" in res.stdout
