@@ -580,6 +580,14 @@ void fluid_multi_destroy(FluidMulti* h) {
     if (!h) return;
     Multi* m = reinterpret_cast<Multi*>(h);
     for (Band* b : m->bands) if (b && b->sim && b->sim->stream) { cudaSetDevice(b->sim->device); cudaStreamSynchronize(b->sim->stream); }
+    if (m->transport == FLUID_TRANSPORT_PEER && !m->bands.empty() && m->bands[0] && m->bands[0]->comm && m->bands[0]->scratch_word) {
+        // PEER: the other ranks read this rank's boxes through their IPC mappings; memory exported through CUDA IPC may only be
+        // freed once the importers are done with it. Destruction is therefore collective, like creation: a barrier (an
+        // all-gather of one word) after every rank has drained its own stream — its last pull included.
+        Band* b = m->bands[0];
+        uint32_t* w = reinterpret_cast<uint32_t*>(b->scratch_word);
+        if (g_nccl.AllGather(w, w + 4, 1, ncclUint32, b->comm, b->sim->stream) == ncclSuccess) cudaStreamSynchronize(b->sim->stream);
+    }
     for (Band* b : m->bands) band_free(b);
     delete m;
 }

@@ -276,7 +276,7 @@ int fluid_multi_create(const FluidSimSettings* settings, int n_ranks, const int*
 int fluid_multi_unique_id(uint8_t out[FLUID_MULTI_ID_BYTES]);
 int fluid_multi_create_rank(const FluidSimSettings* settings, int rank, int world, const uint8_t id[FLUID_MULTI_ID_BYTES], int device,
                             const FluidMultiOptions* opt, FluidMulti** out);
-void fluid_multi_destroy(FluidMulti* m);
+void fluid_multi_destroy(FluidMulti* m); /* FLUID_TRANSPORT_PEER: collective over the ranks, like creation (the ranks read each other's memory) */
 /* reference: `FluidSimulation::tick` (src/simulation.rs:459-539); asynchronous on every band's stream */
 int fluid_multi_tick(FluidMulti* m, const FluidTickSettings* tick);
 int fluid_multi_tick_n(FluidMulti* m, const FluidTickSettings* tick, uint32_t n);
