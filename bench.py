@@ -215,7 +215,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-also", action="store_true", help="skip the short 1M / default-scene / fast-math timings appended to the line")
     ap.add_argument("--no-parity", action="store_true", help="--gpus > 1: skip the NCCL-path-vs-single-GPU parity check before timing")
-    ap.add_argument("--e2e-steps", type=int, default=20,
+    ap.add_argument("--e2e-steps", type=int, default=40,
                     help="steps of the end-to-end loop; its timed region includes filling and draining the transfer pipeline (one full "
                          "download after the last tick), which 6 steps did not amortise: 48.7 ms per step at 64M against a cadence of 42.3")
     args = ap.parse_args()
