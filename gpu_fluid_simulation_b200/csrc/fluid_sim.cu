@@ -151,7 +151,14 @@ void Sim::make_uniform(const FluidTickSettings& t, uint32_t tick_value, FluidSim
 // tiles from both ends of the key order while the neighbour passes are a few dozen waves of CTAs (kernels_sph.cuh
 // tile_from_both_ends); measured: 1M dam break -13 % early, -21 % after 320 ticks; no gain on the 64M uniform box
 constexpr uint32_t TILES_BOTH_ENDS_MAX = 16384;  // 4M particles: ~28 waves of 592 resident CTAs (balanced scenes pay ~2 % for the order: 1M-U, 8M-particle bands)
-bool Sim::tiles_both_ends() const { return tile_order >= 0 ? tile_order != 0 : capacity / SPH_THREADS <= TILES_BOTH_ENDS_MAX; }
+// ... and only while some cell is crowded: the scan publishes the largest cell population into pinned host memory every
+// counted tick (read here without synchronising: it lags by the ticks in flight, which only delays the switch). A balanced
+// scene (1M-U: largest cell ~8 of a mean of 4) keeps the index order, which is 2 % faster there.
+constexpr uint32_t TILES_BOTH_ENDS_MIN_CELL = 10;  // (1M-D crosses it ~35 ticks in, 1M-U never: its largest cell stays at 8)
+bool Sim::tiles_both_ends() const {
+    if (tile_order >= 0) return tile_order != 0;
+    return capacity / SPH_THREADS <= TILES_BOTH_ENDS_MAX && cell_max_host && cell_max_host[0] >= TILES_BOTH_ENDS_MIN_CELL;
+}
 DevParams Sim::make_params(const FluidSimUniform& u) const {
     DevParams p;
     memset(&p, 0, sizeof p);
