@@ -93,3 +93,21 @@ def test_scenes_deterministic(fluid):
     assert p["position"][:, 0].max() < -s.size[0] / 4 + 0.05
     r = scenes.splitmix64(1, 4)
     assert (r >= 0).all() and (r < 1).all() and len(set(r.tolist())) == 4
+
+
+def test_header_constants_match_the_python_mirror(fluid):
+    """the #defines a C / Rust host reads are the numbers the Python mirror uses (transports, limits, ABI version)."""
+    import re
+    from gpu_fluid_simulation_b200 import jfa, multi
+    with open(os.path.join(ROOT, "include", "fluid_b200.h")) as f:
+        text = f.read()
+    defs = {m.group(1): m.group(2) for m in re.finditer(r"^#define\s+(FLUID_\w+)\s+\(?([0-9a-fxu<> ]+?)\)?\s*(?:/\*.*)?$", text, flags=re.M)}
+
+    def val(name):
+        return int(eval(defs[name].replace("u", "")))  # "1u << 20" -> 1 << 20
+    assert val("FLUID_TRANSPORT_AUTO") == multi.TRANSPORT_AUTO
+    assert val("FLUID_TRANSPORT_NCCL") == multi.TRANSPORT_NCCL
+    assert val("FLUID_TRANSPORT_LOCAL") == multi.TRANSPORT_LOCAL
+    assert val("FLUID_TRANSPORT_PEER") == multi.TRANSPORT_PEER
+    assert val("FLUID_JFA_STATIC_MAX_PIXELS") == jfa.JFA_STATIC_MAX_PIXELS
+    assert val("FLUID_MULTI_MAX_RANKS") == 8
