@@ -73,6 +73,14 @@ extern "C" {
     fn fluid_multi_download_start_indices(m: *mut FluidMulti, dst: *mut u32) -> c_int;
     fn fluid_multi_upload_force_field(m: *mut FluidMulti, xy: *const f32) -> c_int;
     fn fluid_multi_particle_counts(m: *mut FluidMulti, counts: *mut u32) -> c_int;
+    // jump flood in the library's static device scratch (no allocation in the call; at most 2^20 pixels; not in the reference)
+    fn fluid_jfa_run_static(seeds_in: *const u32, w: u32, h: u32, seeds_out: *mut u32, device_ordinal: c_int, stream: *mut c_void, wait: c_int) -> c_int;
+}
+
+/// `fluid_jfa_run` for hosts that may not allocate device memory: `seeds` is an rg32uint image (w*h pairs), host or device memory.
+pub fn jfa_run_static(seeds: &[u32], w: u32, h: u32, out: &mut [u32], device: i32) {
+    assert!(seeds.len() == (w as usize) * (h as usize) * 2 && out.len() == seeds.len());
+    check(unsafe { fluid_jfa_run_static(seeds.as_ptr(), w, h, out.as_mut_ptr(), device as c_int, std::ptr::null_mut(), 1) });
 }
 
 fn check(rc: c_int) {
