@@ -225,6 +225,12 @@ k_band_rank_gather(const DevParams p, const BandRows rows, uint32_t key_lo, uint
     }
 }
 
+// a key pass that was run ahead by the force pass and is NOT used (the next tick came with another delta): its pushes are
+// forgotten before the key pass proper runs (the records it stored are overwritten from slot 0)
+__global__ void k_band_forget_pushes(BandDyn* __restrict__ dyn) {
+    if (threadIdx.x < BAND_MAX_RANKS) { dyn->out_count[threadIdx.x] = 0u; dyn->e_row[threadIdx.x] = 0u; }
+}
+
 // ---- pipelined host transfers of a band (fluid_multi_upload_band_async / _download_band_async) -------------------------
 __global__ void k_band_set_word(uint32_t* __restrict__ w, uint32_t v) { *w = v; }
 // after an upload whose sizes were all-gathered on the device: the counters band_set_counts writes from the host

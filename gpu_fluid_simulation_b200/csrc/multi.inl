@@ -282,7 +282,13 @@ static int band_enqueue_key(Multi* m, Band* b, const FluidTickSettings& t, DevPa
     const bool hit = b->spec_valid && !b->explicit_origins && memcmp(&b->spec_delta, &t.delta, sizeof(float)) == 0;
     b->spec_valid = false;
     if (!hit) {
-        if (b->count_dirty) FLUID_CUDA(cudaMemsetAsync(s->cell_count, 0, (size_t)b->bin_tiles * CELL_SCAN_TILE * 4, s->stream));  // unused speculation
+        if (b->count_dirty) {  // unused speculation: drop its histogram and its pushes into the outboxes
+            FLUID_CUDA(cudaMemsetAsync(s->cell_count, 0, (size_t)b->bin_tiles * CELL_SCAN_TILE * 4, s->stream));
+#ifndef FLUID_AB_NO_FORGET  // (A/B builds only: shows that tests/test_gpu_multi.py::test_changing_delta_* needs this launch)
+            k_band_forget_pushes<<<1, 32, 0, s->stream>>>(b->dyn);
+            s->launches++;
+#endif
+        }
         uint32_t blocks = (b->capacity + BAND_KEY_THREADS - 1) / BAND_KEY_THREADS;
         const uint32_t max_blocks = (uint32_t)s->num_sms * 8u;
         if (blocks > max_blocks) blocks = max_blocks;

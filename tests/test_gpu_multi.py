@@ -147,6 +147,26 @@ def test_stale_table_quirk_bands(fluid):
         _assert_identical(got, tab, want, want_table)
 
 
+def test_changing_delta_drops_the_speculated_key_pass(fluid):
+    """the reference's delta is the frame time and changes every frame (src/main.rs: delta from the clock): the key pass that the
+    force pass ran ahead with the old delta — keys, histogram, copies for the other ranks — must be dropped, not added to."""
+    from gpu_fluid_simulation_b200 import multi
+    s, ts, p = scenes.dam_break(48, 256)
+    ts.gravity = (3.0, 9.8)
+    deltas = [1 / 120, 1 / 120, 1 / 90, 1 / 144, 1 / 144, 1 / 60, 1 / 120]
+    for world in (2, 5):
+        with multi.MultiFluidSimulation.new([0] * world, s, transport=multi.TRANSPORT_LOCAL, window_near=16384) as m, \
+                fluid.FluidSimulation.new(0, s) as ref:
+            m.upload_particles(p)
+            ref.upload_particles(p)
+            for d in deltas:
+                ts.delta = d
+                ref.tick(ts)
+                m.tick(ts)
+            m.sync()
+            _assert_identical(m.download_particles(), m.download_start_indices(), ref.download_particles(), ref.download_start_indices())
+
+
 def test_custom_and_balanced_row_bounds(fluid):
     from gpu_fluid_simulation_b200 import multi
     s, ts, p = scenes.dam_break(40, 200)
