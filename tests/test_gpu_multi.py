@@ -148,8 +148,8 @@ def test_stale_table_quirk_bands(fluid):
 
 
 def test_changing_delta_drops_the_speculated_key_pass(fluid):
-    """the reference's delta is the frame time and changes every frame (src/main.rs: delta from the clock): the key pass that the
-    force pass ran ahead with the old delta — keys, histogram, copies for the other ranks — must be dropped, not added to."""
+    """the reference's delta is a setting the user can drag while the simulation runs (src/renderer.rs:642-644), so it can differ
+    between two ticks: the key pass that the force pass ran ahead with the old delta — keys, histogram, copies for the other ranks — must be dropped, not added to."""
     from gpu_fluid_simulation_b200 import multi
     s, ts, p = scenes.dam_break(48, 256)
     ts.gravity = (3.0, 9.8)
